@@ -1,0 +1,222 @@
+/*
+ * otedama_b200.h — C ABI of libotedama_b200.so: a B200 (sm_100a) SHA-256d
+ * proof-of-work search engine that drops in behind Otedama's
+ * internal/miner worker / internal/hal device interface.
+ *
+ * The reference (shizukutanaka/Otedama) is pure Go and has no FFI today; every
+ * entry point below names the Go symbol a cgo shim would route to it (paths are
+ * relative to the reference tree).  INTEGRATION.md shows that shim.
+ *
+ * Conventions: plain C types only; opaque handles; caller-allocated outputs;
+ * every function returning int yields 0 (or a count) on success and a negative
+ * OTD_E* code on failure, with a per-thread message behind otd_last_error().
+ * Hash/target byte order is the reference's miner.Hash: 32 bytes, little-endian
+ * integer, most significant byte at index 31 (internal/miner/sha256d.go:84-103).
+ * There is no CPU fallback: without a usable CUDA device the compute entry
+ * points fail with OTD_ENODEV.
+ */
+#ifndef OTEDAMA_B200_H
+#define OTEDAMA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OTD_OK 0
+#define OTD_EINVAL (-22)
+#define OTD_ENODEV (-19)
+#define OTD_ENOMEM (-12)
+#define OTD_EBUSY (-16)
+#define OTD_ECUDA (-5)
+#define OTD_ERANGE (-34)
+
+#define OTD_ABI_VERSION 1
+
+/* Last error message of the calling thread ("" if none). Never NULL. */
+const char* otd_last_error(void);
+int otd_abi_version(void);
+
+/* ---------------------------------------------------------------- devices --
+ * Replaces hal.Driver.Enumerate / hal.Device.Identity / Capabilities
+ * (internal/hal/device.go:155-198) for a new "cuda" driver registered next to
+ * GPULinuxDriver in engine.detectDevices (internal/engine/setup.go:29-54). */
+typedef struct {
+    char id[32];          /* hal.Identity.ID, e.g. "gpu-cuda0" (no whitespace or '/') */
+    char model[128];      /* hal.Identity.Model */
+    char vendor[16];      /* hal.Identity.Vendor: "nvidia" */
+    char pci_bus_id[32];
+    int32_t sm_count;
+    int32_t cc_major, cc_minor;
+    int32_t sm_clock_khz;
+    uint64_t total_mem_bytes;
+    int32_t cap_sha256d;          /* hal.Capabilities.SHA256d        (1 on sm_100) */
+    int32_t cap_general_compute;  /* hal.Capabilities.GeneralCompute (1) */
+} otd_device_info_t;
+
+int otd_device_count(void);                               /* >= 0, or OTD_E* */
+int otd_device_info(int device_index, otd_device_info_t* out);
+
+/* ------------------------------------------------------------ header math --
+ * Host-side mirrors of internal/miner/sha256d.go helpers (once per job). */
+typedef struct {            /* miner.Header, sha256d.go:49-56 */
+    uint32_t version;
+    uint8_t prev_hash[32];
+    uint8_t merkle_root[32];
+    uint32_t time;
+    uint32_t bits;
+    uint32_t nonce;
+} otd_header_t;
+
+void otd_header_bytes(const otd_header_t* h, uint8_t out[80]);      /* Header.Bytes   :59-68  */
+void otd_parse_header(const uint8_t in[80], otd_header_t* h);       /* ParseHeader    :71-80  */
+int otd_hash_less_or_equal(const uint8_t h[32], const uint8_t other[32]); /* LessOrEqual :93-103 */
+int otd_target_from_nbits(uint32_t nbits, uint8_t target[32]);      /* TargetFromNBits :134-173 */
+uint32_t otd_nbits_from_target(const uint8_t target[32]);           /* NBitsFromTarget :178-205 */
+int otd_target_from_difficulty(double difficulty, uint8_t target[32]); /* TargetFromDifficulty :226-247 */
+/* MeetsTarget :251-257 — returns 1/0, or OTD_EINVAL for malformed nbits */
+int otd_meets_target(const uint8_t hash[32], uint32_t nbits);
+
+/* GPU batch form of miner.HashHeader / miner.SHA256d on 80-byte inputs
+ * (sha256d.go:107-117): hashes n serialised headers (host pointers) on
+ * `device_index`, writes n*32 bytes. */
+int otd_hash_headers(int device_index, const uint8_t* headers80, size_t n, uint8_t* hashes32);
+
+/* ------------------------------------------------------------------- work --
+ * miner.Work (internal/miner/worker.go:18-24) plus the search-space extension
+ * north_star asks for.  A zero-initialised extension reproduces the reference:
+ * one header, nonce-only search of all 2^32 nonces. */
+#define OTD_WORK_REPEAT 1u /* when the space is exhausted start over (the reference's
+                              uint32 wrap, worker.go:279) instead of going idle */
+
+typedef struct {
+    uint32_t job_id;      /* Work.JobID     */
+    uint32_t channel_id;  /* Work.ChannelID */
+    otd_header_t header;  /* Work.Header (nonce ignored) */
+    uint32_t nbits;       /* Work.NBits     */
+    uint8_t target[32];   /* Work.Target — the SHARE target */
+
+    uint32_t flags;
+    /* nonce window: [nonce_begin, nonce_begin + nonce_count); nonce_count 0 = 2^32 */
+    uint32_t nonce_begin;
+    uint64_t nonce_count;
+    /* BIP-320 version rolling: version_mask 0 = off.  Rolled version index
+     * k = version_begin + i*version_stride, i in [0, version_count);
+     * version_count 0 with a mask = all 2^popcount(mask) indices from
+     * version_begin; stride 0 = 1.  (Static partition over G GPUs: begin = g,
+     * stride = G.) */
+    uint32_t version_mask;
+    uint32_t version_begin, version_count, version_stride;
+    /* Stratum V1 coinbase: coinb1 NULL = off (header.merkle_root is used).
+     * coinbase = coinb1 || extranonce1 || extranonce2 || coinb2, extranonce2 =
+     * little-endian counter of extranonce2_size (<= 8) bytes, value
+     * e = extranonce2_begin + i*extranonce2_stride, i in [0, extranonce2_count).
+     * merkle_branches = n_branches * 32 bytes.  Buffers are copied. */
+    const uint8_t* coinb1;
+    uint32_t coinb1_len;
+    const uint8_t* extranonce1;
+    uint32_t extranonce1_len;
+    const uint8_t* coinb2;
+    uint32_t coinb2_len;
+    const uint8_t* merkle_branches;
+    uint32_t n_branches;
+    uint32_t extranonce2_size;
+    uint64_t extranonce2_begin, extranonce2_count, extranonce2_stride;
+} otd_work_t;
+
+typedef struct {          /* miner.Share, worker.go:33-43 */
+    uint32_t channel_id;
+    uint32_t job_id;
+    uint32_t nonce;
+    uint32_t ntime;
+    uint32_t version;     /* the exact (rolled) version that was hashed */
+    uint8_t hash[32];
+    uint64_t extranonce2; /* value rolled into the coinbase (0 when unused) */
+    uint64_t work_seq;    /* which set_work call this share belongs to (1-based) */
+    int32_t device_index; /* -> Share.DeviceID via otd_device_info().id */
+    int32_t reserved;
+} otd_share_t;
+
+/* ----------------------------------------------------------------- worker --
+ * One worker per device: the GPU counterpart of *miner.Worker
+ * (internal/miner/worker.go:91-212), constructed by engine.startMinerWorkers
+ * (internal/engine/setup.go:59-77) for every device with SHA256d capability. */
+typedef struct otd_worker otd_worker_t;
+
+typedef struct {
+    uint32_t ring_capacity;   /* device share ring entries per launch; 0 = 4096 */
+    uint32_t queue_capacity;  /* host share queue (reference: chan cap Threads*4); 0 = 65536.
+                                 Shares arriving at a full queue are dropped and counted. */
+    uint32_t launch_log2;     /* nonces per kernel launch = 2^launch_log2 (16..32); 0 = 32 */
+    int32_t kernel_variant;   /* scan kernel variant, -1 = library default (see otd_scan_variants) */
+} otd_worker_config_t;
+
+typedef struct {            /* miner.Stats, worker.go:79-86, plus device extras */
+    uint64_t hashes_total;
+    uint64_t shares_found;
+    uint64_t shares_dropped;
+    uint64_t uptime_ns;
+    double hash_rate;         /* lifetime average, like the reference */
+    uint64_t launches;        /* scan kernel launches completed */
+    uint64_t candidates;      /* candidates that passed the top-word test (slow path runs) */
+    double device_ms;         /* scan-kernel time on the device (CUDA events) */
+    uint64_t work_seq;        /* current set_work generation */
+    int32_t has_work;         /* Worker.HasWork() */
+    int32_t exhausted;        /* 1 when the current work's search space is finished */
+} otd_stats_t;
+
+/* NewWorker + Start (worker.go:111-151).  cfg may be NULL. Returns NULL on error. */
+otd_worker_t* otd_worker_create(int device_index, const otd_worker_config_t* cfg);
+/* SetWork (worker.go:171-176). work == NULL pauses (idle). The work and its
+ * buffers are copied; safe from any thread. Returns the new work_seq (> 0). */
+int64_t otd_worker_set_work(otd_worker_t* w, const otd_work_t* work);
+/* The receive side of Start's `<-chan Share`: blocks up to timeout_ms
+ * (0 = poll, < 0 = forever) until at least one share is available, the current
+ * work is exhausted, or the worker is destroyed.  Returns the count written. */
+int otd_worker_poll_shares(otd_worker_t* w, otd_share_t* out, int max_shares, int timeout_ms);
+/* Blocks until the current work is exhausted (or timeout). 1 = exhausted, 0 = timeout. */
+int otd_worker_wait_exhausted(otd_worker_t* w, int timeout_ms);
+int otd_worker_stats(otd_worker_t* w, otd_stats_t* out);        /* Stats()   worker.go:189-212 */
+int otd_worker_has_work(otd_worker_t* w);                       /* HasWork() worker.go:181-185 */
+int otd_worker_device_index(otd_worker_t* w);                   /* DeviceID() worker.go:176    */
+/* Stop (worker.go:156-165): aborts in-flight work, joins the host thread, frees. */
+int otd_worker_destroy(otd_worker_t* w);
+
+/* ------------------------------------------------------- synchronous scan --
+ * One pass of grind (worker.go:216-282) over `work`'s whole search space on one
+ * device, returning when done: the call tests and benchmarks use.  Writes up to
+ * max_shares shares (sorted by extranonce2, version, nonce); *n_found gets the
+ * total found (may exceed max_shares).  Optional outputs may be NULL:
+ * *hashes = candidates hashed, *device_ms = scan-kernel time by CUDA events on
+ * the launching stream, *launches = scan kernel launches. */
+int otd_scan(int device_index, const otd_work_t* work, int kernel_variant, otd_share_t* out,
+             uint32_t max_shares, uint64_t* n_found, uint64_t* hashes, double* device_ms,
+             uint64_t* launches);
+
+/* Kernel variants compiled into the library: returns the count, fills
+ * names[i] (each up to 32 bytes incl. NUL) when names != NULL. */
+int otd_scan_variants(char (*names)[32], int max_names);
+
+/* Job-preparation kernels exposed for parity tests (K3: extranonce2 roll +
+ * coinbase hash + merkle fold; K2: rolled version). Fills n merkle roots
+ * (32 bytes each) / n versions for the work's first n instances. */
+int otd_prepare_instances(int device_index, const otd_work_t* work, uint32_t first, uint32_t n,
+                          uint8_t* merkle_roots, uint32_t* versions, uint64_t* extranonce2s,
+                          uint8_t* midstates /* n*32 bytes, BE words as bytes; may be NULL */);
+
+/* ---------------------------------------------------- integer-issue peak --
+ * Measures the sustained integer instruction rate of the device (the roofline
+ * this path is bound by).  mode: see otd_int_peak_modes.  Returns thread-level
+ * integer ops per second in *ops_per_s (instructions of the named class per
+ * thread, summed over the chip) and the SM clock seen (*sm_mhz, from clock64
+ * ticks over event time). */
+int otd_int_peak(int device_index, int mode, int iters, double* ops_per_s, double* sm_mhz,
+                 double* ms);
+int otd_int_peak_modes(char (*names)[32], int max_names);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OTEDAMA_B200_H */

@@ -1,0 +1,117 @@
+// intpeak.cuh — integer-issue roofline microbenchmark for sm_100a.
+//
+// The SHA-256d scan is bound by integer instruction issue (SHF / LOP3 / IADD3 on
+// the ALU pipe, optionally IMAD on the FMA pipe), not by HBM or tensor cores, so
+// the roofline denominator has to be measured on the same chip: each mode runs
+// NCH independent dependency chains per thread of one instruction class (or of
+// the SHA mix) with no memory traffic and reports thread-level ops per second.
+#pragma once
+#include <stdint.h>
+
+namespace otd {
+
+enum IntPeakMode {
+    IPM_LOP3 = 0,      // lop3.b32 chains                               (ALU pipe)
+    IPM_SHF = 1,       // shf.r.wrap chains                             (ALU pipe)
+    IPM_IADD3 = 2,     // 3-input add chains                            (ALU pipe)
+    IPM_IMAD = 3,      // mad.lo.u32 with a runtime multiplier          (FMA pipe)
+    IPM_MIX_ALU = 4,   // SHA mix: 2 SHF : 1 LOP3 : 1 IADD3, all ALU
+    IPM_MIX_DUAL = 5,  // SHA mix, the 3-input add done as two IMADs    (ALU + FMA)
+    IPM_MIX_DUAL1 = 6, // 2 SHF : 1 LOP3 : 1 IMAD (a 2-input add)        (ALU + FMA)
+    IPM_IMAD_WIDE = 7, // mul.wide.u32 chains                           (FMA pipe, 64-bit result)
+    IPM_PRMT = 8,      // prmt chains                                   (ALU pipe)
+    IPM_ALU_FMA = 9,   // 1 LOP3 : 1 IMAD interleaved                   (both pipes)
+    IPM_COUNT = 10
+};
+
+#if defined(__CUDACC__)
+
+constexpr int kIpChains = 8;
+constexpr int kIpUnroll = 16;
+
+// thread-level ops of the counted class per (chain, unroll step)
+__host__ __device__ constexpr int ip_ops_per_step(int mode)
+{
+    return (mode == IPM_MIX_ALU || mode == IPM_MIX_DUAL || mode == IPM_MIX_DUAL1) ? 4
+           : (mode == IPM_ALU_FMA)                                                ? 2
+                                                                                  : 1;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) int_peak_kernel(int iters, uint32_t one, uint32_t seed,
+                                                       uint32_t* sink, long long* cycles)
+{
+    uint32_t x[kIpChains], y[kIpChains], z[kIpChains];
+#pragma unroll
+    for (int c = 0; c < kIpChains; c++) {
+        x[c] = seed + threadIdx.x * 2654435761u + c * 40503u;
+        y[c] = x[c] ^ 0x9e3779b9u;
+        z[c] = x[c] * 3u + 1u;
+    }
+    const long long t0 = clock64();
+#pragma unroll 1
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < kIpUnroll; u++) {
+#pragma unroll
+            for (int c = 0; c < kIpChains; c++) {
+                if (MODE == IPM_LOP3) {
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                } else if (MODE == IPM_SHF) {
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
+                } else if (MODE == IPM_IADD3) {
+                    asm volatile("{ .reg .u32 t; add.u32 t, %0, %1; add.u32 %0, t, %2; }"
+                                 : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                } else if (MODE == IPM_IMAD) {
+                    asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x[c]) : "r"(one), "r"(y[c]));
+                } else if (MODE == IPM_MIX_ALU) {
+                    asm volatile(
+                        "{ .reg .u32 t, s;\n"
+                        "shf.r.wrap.b32 t, %0, %0, 6;\n"
+                        "shf.r.wrap.b32 s, %0, %0, 11;\n"
+                        "lop3.b32 %1, %0, t, s, 0x96;\n"
+                        "add.u32 t, %0, %1;\n"
+                        "add.u32 %0, t, %2; }"
+                        : "+r"(x[c]), "+r"(y[c]) : "r"(z[c]));
+                } else if (MODE == IPM_MIX_DUAL) {
+                    asm volatile(
+                        "{ .reg .u32 t, s;\n"
+                        "shf.r.wrap.b32 t, %0, %0, 6;\n"
+                        "shf.r.wrap.b32 s, %0, %0, 11;\n"
+                        "lop3.b32 %1, %0, t, s, 0x96;\n"
+                        "mad.lo.u32 t, %0, %3, %1;\n"
+                        "mad.lo.u32 %0, t, %3, %2; }"
+                        : "+r"(x[c]), "+r"(y[c]) : "r"(z[c]), "r"(one));
+                } else if (MODE == IPM_MIX_DUAL1) {
+                    asm volatile(
+                        "{ .reg .u32 t, s;\n"
+                        "shf.r.wrap.b32 t, %0, %0, 6;\n"
+                        "shf.r.wrap.b32 s, %0, %0, 11;\n"
+                        "lop3.b32 %1, %0, t, s, 0x96;\n"
+                        "mad.lo.u32 %0, %0, %2, %1; }"
+                        : "+r"(x[c]), "+r"(y[c]) : "r"(one));
+                } else if (MODE == IPM_IMAD_WIDE) {
+                    asm volatile(
+                        "{ .reg .u64 w;\n"
+                        "mul.wide.u32 w, %0, %2;\n"
+                        "mov.b64 {%0, %1}, w; }"
+                        : "+r"(x[c]), "=r"(y[c]) : "r"(one));
+                } else if (MODE == IPM_PRMT) {
+                    asm volatile("prmt.b32 %0, %0, %1, 0x0321;" : "+r"(x[c]) : "r"(y[c]));
+                } else if (MODE == IPM_ALU_FMA) {
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(z[c]));
+                }
+            }
+        }
+    }
+    const long long t1 = clock64();
+    uint32_t acc = 0;
+#pragma unroll
+    for (int c = 0; c < kIpChains; c++) acc ^= x[c] ^ y[c] ^ z[c];
+    if (acc == 0x12345678u) sink[0] = acc;  // keep the chains alive
+    if (blockIdx.x == 0 && threadIdx.x == 0) cycles[0] = t1 - t0;
+}
+
+#endif
+}  // namespace otd

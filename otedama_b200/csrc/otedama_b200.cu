@@ -1,0 +1,1067 @@
+// otedama_b200.cu — libotedama_b200.so: host runtime + C ABI over the sm_100a
+// kernels (scan_kernel.cuh, job_kernels.cuh, intpeak.cuh).
+//
+// Host side mirrors internal/miner.Worker (internal/miner/worker.go:91-282): one
+// worker per device owns a host thread, a CUDA stream and a pair of device share
+// rings; SetWork swaps the job and bumps a generation, shares flow back through a
+// bounded queue with a drop counter, Stats is a lock-light snapshot.  There is no
+// CPU hashing path in this library: candidates are hashed, confirmed and turned
+// into 32-byte hashes on the device.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <condition_variable>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <functional>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/otedama_b200.h"
+#include "intpeak.cuh"
+#include "job_kernels.cuh"
+#include "scan_kernel.cuh"
+
+using namespace otd;
+
+// ------------------------------------------------------------------ errors --
+static thread_local std::string g_last_error;
+static int fail(int code, const std::string& msg)
+{
+    g_last_error = msg;
+    return code;
+}
+#define CU_TRY(expr)                                                                          \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess)                                                                \
+            return fail(OTD_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));       \
+    } while (0)
+
+extern "C" const char* otd_last_error(void) { return g_last_error.c_str(); }
+extern "C" int otd_abi_version(void) { return OTD_ABI_VERSION; }
+
+// ----------------------------------------------------------------- devices --
+extern "C" int otd_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) {
+        cudaGetLastError();
+        return 0;
+    }
+    if (e != cudaSuccess) return fail(OTD_ECUDA, std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e));
+    return n;
+}
+
+static int check_device(int idx)
+{
+    int n = otd_device_count();
+    if (n < 0) return n;
+    if (n == 0) return fail(OTD_ENODEV, "no CUDA device available (this library has no CPU fallback)");
+    if (idx < 0 || idx >= n) return fail(OTD_ENODEV, "device index " + std::to_string(idx) + " out of range");
+    return OTD_OK;
+}
+
+extern "C" int otd_device_info(int idx, otd_device_info_t* out)
+{
+    if (!out) return fail(OTD_EINVAL, "otd_device_info: out is NULL");
+    int rc = check_device(idx);
+    if (rc) return rc;
+    cudaDeviceProp p;
+    CU_TRY(cudaGetDeviceProperties(&p, idx));
+    memset(out, 0, sizeof *out);
+    snprintf(out->id, sizeof out->id, "gpu-cuda%d", idx);
+    snprintf(out->model, sizeof out->model, "%s", p.name);
+    snprintf(out->vendor, sizeof out->vendor, "nvidia");
+    char bus[32] = {0};
+    if (cudaDeviceGetPCIBusId(bus, sizeof bus, idx) == cudaSuccess) snprintf(out->pci_bus_id, sizeof out->pci_bus_id, "%s", bus);
+    out->sm_count = p.multiProcessorCount;
+    out->cc_major = p.major;
+    out->cc_minor = p.minor;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, idx);
+    out->sm_clock_khz = khz;
+    out->total_mem_bytes = p.totalGlobalMem;
+    // the kernels are built for sm_100a only
+    out->cap_sha256d = (p.major == 10) ? 1 : 0;
+    out->cap_general_compute = 1;
+    return OTD_OK;
+}
+
+// ------------------------------------------------------------- header math --
+static inline void put_le32(uint8_t* p, uint32_t v) { p[0] = v; p[1] = v >> 8; p[2] = v >> 16; p[3] = v >> 24; }
+static inline uint32_t get_le32(const uint8_t* p)
+{
+    return (uint32_t)p[0] | (uint32_t)p[1] << 8 | (uint32_t)p[2] << 16 | (uint32_t)p[3] << 24;
+}
+
+extern "C" void otd_header_bytes(const otd_header_t* h, uint8_t out[80])
+{
+    put_le32(out, h->version);
+    memcpy(out + 4, h->prev_hash, 32);
+    memcpy(out + 36, h->merkle_root, 32);
+    put_le32(out + 68, h->time);
+    put_le32(out + 72, h->bits);
+    put_le32(out + 76, h->nonce);
+}
+extern "C" void otd_parse_header(const uint8_t in[80], otd_header_t* h)
+{
+    h->version = get_le32(in);
+    memcpy(h->prev_hash, in + 4, 32);
+    memcpy(h->merkle_root, in + 36, 32);
+    h->time = get_le32(in + 68);
+    h->bits = get_le32(in + 72);
+    h->nonce = get_le32(in + 76);
+}
+extern "C" int otd_hash_less_or_equal(const uint8_t h[32], const uint8_t o[32])
+{
+    for (int i = 31; i >= 0; i--) {
+        if (h[i] < o[i]) return 1;
+        if (h[i] > o[i]) return 0;
+    }
+    return 1;
+}
+
+// Small unsigned big integer (little-endian 32-bit limbs) for the once-per-job
+// target conversions (the reference uses math/big).
+struct BigU {
+    static const int N = 24;  // 768 bits
+    uint32_t v[N];
+    BigU() { memset(v, 0, sizeof v); }
+    int bit_length() const
+    {
+        for (int i = N - 1; i >= 0; i--)
+            if (v[i]) return 32 * i + (32 - __builtin_clz(v[i]));
+        return 0;
+    }
+    bool is_zero() const { return bit_length() == 0; }
+    void shl(int s)
+    {
+        int ws = s / 32, bs = s % 32;
+        uint32_t r[N] = {0};
+        for (int i = N - 1; i >= ws; i--) {
+            uint64_t x = (uint64_t)v[i - ws] << bs;
+            if (bs && i - ws - 1 >= 0) x |= v[i - ws - 1] >> (32 - bs);
+            r[i] = (uint32_t)x;
+        }
+        memcpy(v, r, sizeof v);
+    }
+    void shr(int s)
+    {
+        int ws = s / 32, bs = s % 32;
+        uint32_t r[N] = {0};
+        for (int i = 0; i + ws < N; i++) {
+            uint64_t x = v[i + ws] >> bs;
+            if (bs && i + ws + 1 < N) x |= (uint64_t)v[i + ws + 1] << (32 - bs);
+            r[i] = (uint32_t)x;
+        }
+        memcpy(v, r, sizeof v);
+    }
+    bool low_bits_nonzero(int s) const  // any of the low s bits set
+    {
+        for (int i = 0; i < N && 32 * i < s; i++) {
+            uint32_t m = (s - 32 * i >= 32) ? 0xffffffffu : ((1u << (s - 32 * i)) - 1u);
+            if (v[i] & m) return true;
+        }
+        return false;
+    }
+    bool bit(int i) const { return (v[i / 32] >> (i % 32)) & 1u; }
+    void add1()
+    {
+        for (int i = 0; i < N; i++)
+            if (++v[i]) break;
+    }
+    uint64_t divmod_u64(uint64_t d)  // this /= d, returns remainder
+    {
+        unsigned __int128 rem = 0;
+        for (int i = N - 1; i >= 0; i--) {
+            unsigned __int128 cur = (rem << 32) | v[i];
+            v[i] = (uint32_t)(cur / d);
+            rem = cur % d;
+        }
+        return (uint64_t)rem;
+    }
+};
+
+extern "C" int otd_target_from_nbits(uint32_t nbits, uint8_t target[32])
+{
+    char buf[96];
+    const int exp = (int)(nbits >> 24);
+    const uint32_t mant = nbits & 0x007fffffu;
+    if (nbits & 0x00800000u) {
+        snprintf(buf, sizeof buf, "miner: nBits 0x%08X has negative mantissa bit set", nbits);
+        return fail(OTD_EINVAL, buf);
+    }
+    if (exp < 3) {
+        snprintf(buf, sizeof buf, "miner: nBits 0x%08X exponent %d is below minimum 3", nbits, exp);
+        return fail(OTD_EINVAL, buf);
+    }
+    if (mant == 0) {
+        snprintf(buf, sizeof buf, "miner: nBits 0x%08X has zero mantissa", nbits);
+        return fail(OTD_EINVAL, buf);
+    }
+    BigU b;
+    b.v[0] = mant;
+    const int shift = 8 * (exp - 3);
+    if (shift + 23 >= 32 * BigU::N) return fail(OTD_ERANGE, "miner: nBits target overflows 256 bits");
+    b.shl(shift);
+    if (b.bit_length() > 256) {
+        snprintf(buf, sizeof buf, "miner: nBits 0x%08X target overflows 256 bits", nbits);
+        return fail(OTD_ERANGE, buf);
+    }
+    for (int i = 0; i < 8; i++) put_le32(target + 4 * i, b.v[i]);
+    return OTD_OK;
+}
+
+extern "C" uint32_t otd_nbits_from_target(const uint8_t target[32])
+{
+    int len = 32;
+    while (len > 0 && target[len - 1] == 0) len--;  // big-endian magnitude length
+    if (len == 0) return 0;
+    uint8_t b[34];
+    int n = 0;
+    if (target[len - 1] & 0x80) b[n++] = 0;
+    for (int i = len - 1; i >= 0; i--) b[n++] = target[i];
+    uint32_t mant;
+    if (n == 1) mant = b[0];
+    else if (n == 2) mant = (uint32_t)b[0] << 8 | b[1];
+    else mant = (uint32_t)b[0] << 16 | (uint32_t)b[1] << 8 | b[2];
+    return ((uint32_t)(n & 0xff) << 24) | mant;
+}
+
+extern "C" int otd_target_from_difficulty(double difficulty, uint8_t target[32])
+{
+    char buf[96];
+    if (!(difficulty > 0) || std::isinf(difficulty)) {
+        snprintf(buf, sizeof buf, "miner: invalid difficulty %g", difficulty);
+        return fail(OTD_EINVAL, buf);
+    }
+    // difficulty = m * 2^x exactly (m < 2^53).  quotient = 0xffff * 2^(208-x) / m,
+    // rounded to a 256-bit mantissa (nearest even) like a prec-256 big.Float, then
+    // truncated toward zero by Float.Int.
+    int e2;
+    const double fr = std::frexp(difficulty, &e2);
+    uint64_t m = (uint64_t)std::ldexp(fr, 53);
+    int x = e2 - 53;
+    while ((m & 1) == 0) { m >>= 1; x++; }
+    const int S = 352;  // numerator 0xffff<<S: quotient keeps >= 299 bits
+    BigU q;
+    q.v[0] = 0xffffu;
+    q.shl(S);
+    const uint64_t rem = q.divmod_u64(m);
+    const int L = q.bit_length();
+    const int shift = L - 256;  // >= 2
+    const bool sticky = rem != 0;
+    const bool half = q.bit(shift - 1);
+    const bool below = q.low_bits_nonzero(shift - 1) || sticky;
+    BigU mant = q;
+    mant.shr(shift);
+    if (half && (below || mant.bit(0))) mant.add1();
+    // value = mant * 2^(shift + 208 - x - S)
+    const long exp2 = (long)shift + 208 - x - S;
+    if (exp2 > 0) {
+        if (mant.bit_length() + exp2 > 256) {
+            snprintf(buf, sizeof buf, "miner: difficulty %g target overflows 256 bits", difficulty);
+            return fail(OTD_ERANGE, buf);
+        }
+        mant.shl((int)exp2);
+    } else if (exp2 < 0) {
+        if (-exp2 >= 32 * BigU::N) mant = BigU();
+        else mant.shr((int)-exp2);
+    }
+    if (mant.is_zero()) {
+        snprintf(buf, sizeof buf, "miner: difficulty %g produces a non-positive target", difficulty);
+        return fail(OTD_ERANGE, buf);
+    }
+    if (mant.bit_length() > 256) {
+        snprintf(buf, sizeof buf, "miner: difficulty %g target overflows 256 bits", difficulty);
+        return fail(OTD_ERANGE, buf);
+    }
+    for (int i = 0; i < 8; i++) put_le32(target + 4 * i, mant.v[i]);
+    return OTD_OK;
+}
+
+extern "C" int otd_meets_target(const uint8_t hash[32], uint32_t nbits)
+{
+    uint8_t t[32];
+    int rc = otd_target_from_nbits(nbits, t);
+    if (rc) return OTD_EINVAL;
+    return otd_hash_less_or_equal(hash, t);
+}
+
+// ------------------------------------------------------------ scan variants --
+typedef cudaError_t (*scan_launch_fn)(const JobConsts&, uint32_t, unsigned long long, uint32_t, RingHeader*,
+                                      RingEntry*, uint32_t, const unsigned int*, unsigned int, bool,
+                                      cudaStream_t);
+
+template <int V, int ITER>
+static cudaError_t launch_scan(const JobConsts& jc, uint32_t nonce_begin, unsigned long long count,
+                               uint32_t instance, RingHeader* hdr, RingEntry* ent, uint32_t cap,
+                               const unsigned int* stop, unsigned int gen, bool topzero, cudaStream_t st)
+{
+    constexpr unsigned long long tile = (unsigned long long)kScanBlock * V * ITER;
+    const unsigned grid = (unsigned)((count + tile - 1) / tile);
+    if (grid == 0) return cudaSuccess;
+    if (topzero)
+        scan_kernel<V, ITER, true><<<grid, kScanBlock, 0, st>>>(jc, nonce_begin, count, instance, hdr, ent, cap, stop, gen);
+    else
+        scan_kernel<V, ITER, false><<<grid, kScanBlock, 0, st>>>(jc, nonce_begin, count, instance, hdr, ent, cap, stop, gen);
+    return cudaGetLastError();
+}
+
+struct ScanVariant {
+    const char* name;
+    int v, iter;
+    scan_launch_fn fn;
+};
+static const ScanVariant kVariants[] = {
+    {"v1i16", 1, 16, launch_scan<1, 16>},
+    {"v2i8", 2, 8, launch_scan<2, 8>},
+    {"v4i4", 4, 4, launch_scan<4, 4>},
+};
+static const int kNumVariants = (int)(sizeof kVariants / sizeof kVariants[0]);
+static const int kDefaultVariant = 1;
+
+extern "C" int otd_scan_variants(char (*names)[32], int max_names)
+{
+    if (names)
+        for (int i = 0; i < kNumVariants && i < max_names; i++) snprintf(names[i], 32, "%s", kVariants[i].name);
+    return kNumVariants;
+}
+
+// -------------------------------------------------------------- work copy --
+struct WorkCopy {
+    otd_work_t w;
+    std::vector<uint8_t> blob;  // coinb1 || extranonce1 || coinb2 || branches
+    bool has_coinbase = false;
+    uint64_t n_en2 = 1, n_ver = 1, n_inst = 1;
+    uint64_t nonce_count = 1ull << 32;
+    uint32_t ver_stride = 1;
+    uint64_t en2_stride = 1;
+    uint32_t target_le[8];
+};
+
+static int copy_work(const otd_work_t* in, WorkCopy* wc)
+{
+    if (!in) return fail(OTD_EINVAL, "work is NULL");
+    wc->w = *in;
+    const otd_work_t& w = wc->w;
+    wc->nonce_count = w.nonce_count ? w.nonce_count : (1ull << 32);
+    if ((uint64_t)w.nonce_begin + wc->nonce_count > (1ull << 32))
+        return fail(OTD_EINVAL, "nonce window exceeds 2^32");
+    for (int i = 0; i < 8; i++) wc->target_le[i] = get_le32(w.target + 4 * i);
+    // version rolling
+    wc->n_ver = 1;
+    wc->ver_stride = w.version_stride ? w.version_stride : 1;
+    if (w.version_mask) {
+        const uint64_t total = 1ull << __builtin_popcount(w.version_mask);
+        if (w.version_begin >= total) return fail(OTD_EINVAL, "version_begin outside the mask's index space");
+        const uint64_t avail = (total - w.version_begin + wc->ver_stride - 1) / wc->ver_stride;
+        wc->n_ver = w.version_count ? w.version_count : avail;
+        if (wc->n_ver > avail) return fail(OTD_EINVAL, "version_count exceeds the mask's index space");
+    } else if (w.version_count > 1) {
+        return fail(OTD_EINVAL, "version_count > 1 without a version_mask");
+    }
+    // coinbase
+    wc->has_coinbase = w.coinb1 != nullptr;
+    wc->n_en2 = 1;
+    wc->en2_stride = w.extranonce2_stride ? w.extranonce2_stride : 1;
+    if (wc->has_coinbase) {
+        if (w.extranonce2_size > 16) return fail(OTD_EINVAL, "extranonce2_size > 16");
+        if ((w.extranonce1_len && !w.extranonce1) || (w.coinb2_len && !w.coinb2) || (w.n_branches && !w.merkle_branches))
+            return fail(OTD_EINVAL, "NULL coinbase component with non-zero length");
+        if ((uint64_t)w.coinb1_len + w.extranonce1_len + w.coinb2_len > (1u << 20) || w.n_branches > 64)
+            return fail(OTD_EINVAL, "coinbase too large");
+        if (w.extranonce2_count == 0) return fail(OTD_EINVAL, "extranonce2_count must be >= 1 with a coinbase");
+        if (w.extranonce2_size < 8) {
+            const uint64_t lim = 1ull << (8 * w.extranonce2_size);
+            const uint64_t last = w.extranonce2_begin + (w.extranonce2_count - 1) * wc->en2_stride;
+            if (w.extranonce2_begin >= lim || last >= lim || last < w.extranonce2_begin)
+                return fail(OTD_EINVAL, "extranonce2 range does not fit extranonce2_size bytes");
+        }
+        wc->n_en2 = w.extranonce2_count;
+        wc->blob.resize((size_t)w.coinb1_len + w.extranonce1_len + w.coinb2_len + 32ull * w.n_branches);
+        uint8_t* p = wc->blob.data();
+        memcpy(p, w.coinb1, w.coinb1_len); p += w.coinb1_len;
+        if (w.extranonce1_len) memcpy(p, w.extranonce1, w.extranonce1_len);
+        p += w.extranonce1_len;
+        if (w.coinb2_len) memcpy(p, w.coinb2, w.coinb2_len);
+        p += w.coinb2_len;
+        if (w.n_branches) memcpy(p, w.merkle_branches, 32ull * w.n_branches);
+        // the copies own the bytes now
+        wc->w.coinb1 = wc->w.extranonce1 = wc->w.coinb2 = wc->w.merkle_branches = nullptr;
+    }
+    if (wc->n_en2 > (1ull << 62) / wc->n_ver) return fail(OTD_EINVAL, "search space too large");
+    wc->n_inst = wc->n_en2 * wc->n_ver;
+    return OTD_OK;
+}
+
+// ------------------------------------------------------------------ engine --
+struct RunStats {
+    uint64_t hashes = 0, launches = 0, candidates = 0, found = 0, ring_dropped = 0;
+    double kernel_ms = 0, span_ms = 0;
+};
+
+struct ShareSink {
+    virtual void on_share(const otd_share_t& s) = 0;
+    virtual void on_launch_done(uint64_t hashes, uint64_t candidates, double ms) = 0;
+    virtual ~ShareSink() {}
+};
+
+struct Slot {
+    RingHeader* d_hdr = nullptr;
+    RingEntry* d_ent = nullptr;
+    RingHeader* h_hdr = nullptr;
+    RingEntry* h_ent = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr, edone = nullptr;
+    bool busy = false;
+    uint64_t count = 0, en2 = 0, tile = 0;
+    uint32_t version = 0;
+};
+
+class Engine {
+   public:
+    static const uint32_t kBatch = 256;
+    int dev = -1;
+    uint32_t cap = 0;
+    cudaStream_t stream = nullptr, aux = nullptr;
+    Slot slot[2];
+    unsigned int* d_stop = nullptr;
+    unsigned int* h_gen = nullptr;  // pinned: [0] = run generation, [1] = abort value (0)
+    unsigned int gen = 0;
+    uint8_t* d_blob = nullptr;
+    size_t blob_cap = 0;
+    uint8_t* d_roots = nullptr;
+    JobConsts* d_consts = nullptr;
+    JobConsts* h_consts = nullptr;
+    uint32_t* d_versions = nullptr;
+    uint32_t* h_versions = nullptr;
+    cudaEvent_t ev_first = nullptr, ev_last = nullptr;
+    bool ready = false;
+
+    int init(int device, uint32_t ring_cap)
+    {
+        int rc = check_device(device);
+        if (rc) return rc;
+        dev = device;
+        cap = ring_cap ? ring_cap : 4096;
+        CU_TRY(cudaSetDevice(dev));
+        CU_TRY(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        CU_TRY(cudaStreamCreateWithFlags(&aux, cudaStreamNonBlocking));
+        for (auto& s : slot) {
+            CU_TRY(cudaMalloc(&s.d_hdr, sizeof(RingHeader)));
+            CU_TRY(cudaMalloc(&s.d_ent, sizeof(RingEntry) * (size_t)cap));
+            CU_TRY(cudaMallocHost(&s.h_hdr, sizeof(RingHeader)));
+            CU_TRY(cudaMallocHost(&s.h_ent, sizeof(RingEntry) * (size_t)cap));
+            CU_TRY(cudaEventCreate(&s.e0));
+            CU_TRY(cudaEventCreate(&s.e1));
+            CU_TRY(cudaEventCreate(&s.edone));
+        }
+        CU_TRY(cudaMalloc(&d_stop, sizeof(unsigned int)));
+        CU_TRY(cudaMallocHost(&h_gen, 2 * sizeof(unsigned int)));
+        h_gen[0] = 0; h_gen[1] = 0;
+        CU_TRY(cudaMalloc(&d_roots, 32 * (size_t)kBatch));
+        CU_TRY(cudaMalloc(&d_consts, sizeof(JobConsts) * kBatch));
+        CU_TRY(cudaMallocHost(&h_consts, sizeof(JobConsts) * kBatch));
+        CU_TRY(cudaMalloc(&d_versions, sizeof(uint32_t) * kBatch));
+        CU_TRY(cudaMallocHost(&h_versions, sizeof(uint32_t) * kBatch));
+        CU_TRY(cudaEventCreate(&ev_first));
+        CU_TRY(cudaEventCreate(&ev_last));
+        ready = true;
+        return OTD_OK;
+    }
+
+    void destroy()
+    {
+        if (dev < 0) return;
+        cudaSetDevice(dev);
+        if (stream) cudaStreamSynchronize(stream);
+        if (aux) cudaStreamSynchronize(aux);
+        for (auto& s : slot) {
+            cudaFree(s.d_hdr); cudaFree(s.d_ent); cudaFreeHost(s.h_hdr); cudaFreeHost(s.h_ent);
+            if (s.e0) cudaEventDestroy(s.e0);
+            if (s.e1) cudaEventDestroy(s.e1);
+            if (s.edone) cudaEventDestroy(s.edone);
+            s = Slot();
+        }
+        cudaFree(d_stop); cudaFreeHost(h_gen); cudaFree(d_blob); cudaFree(d_roots); cudaFree(d_consts);
+        cudaFreeHost(h_consts); cudaFree(d_versions); cudaFreeHost(h_versions);
+        if (ev_first) cudaEventDestroy(ev_first);
+        if (ev_last) cudaEventDestroy(ev_last);
+        if (stream) cudaStreamDestroy(stream);
+        if (aux) cudaStreamDestroy(aux);
+        stream = aux = nullptr;
+        d_stop = nullptr; h_gen = nullptr; d_blob = nullptr; d_roots = nullptr; d_consts = nullptr;
+        h_consts = nullptr; d_versions = nullptr; h_versions = nullptr; ev_first = ev_last = nullptr;
+        dev = -1;
+        ready = false;
+    }
+
+    int upload_blob(const WorkCopy& wc)
+    {
+        if (!wc.has_coinbase) return OTD_OK;
+        const size_t need = std::max<size_t>(wc.blob.size(), 1);
+        if (need > blob_cap) {
+            if (d_blob) cudaFree(d_blob);
+            d_blob = nullptr;
+            blob_cap = 0;
+            CU_TRY(cudaMalloc(&d_blob, need));
+            blob_cap = need;
+        }
+        // synchronous small copy: the blob lives in pageable host memory
+        CU_TRY(cudaMemcpyAsync(d_blob, wc.blob.data(), wc.blob.size(), cudaMemcpyHostToDevice, stream));
+        CU_TRY(cudaStreamSynchronize(stream));
+        return OTD_OK;
+    }
+
+    HeaderTemplate make_template(const WorkCopy& wc) const
+    {
+        HeaderTemplate ht;
+        ht.version = wc.w.header.version;
+        ht.version_mask = wc.w.version_mask;
+        memcpy(ht.prev_hash, wc.w.header.prev_hash, 32);
+        memcpy(ht.merkle_root, wc.w.header.merkle_root, 32);
+        ht.time = wc.w.header.time;
+        ht.bits = wc.w.header.bits;
+        memcpy(ht.target, wc.target_le, sizeof ht.target);
+        return ht;
+    }
+
+    // Fill h_consts / h_versions for instances [first, first+n). Leaves the stream idle.
+    int prepare_batch(const WorkCopy& wc, uint64_t first, uint32_t n, uint8_t* roots_out /*host, may be NULL*/)
+    {
+        const bool rolled = wc.has_coinbase || wc.w.version_mask;
+        if (!rolled) {
+            // plain header: midstate and folding once on the host (north_star: "header
+            // midstate ... precomputed once per job on the host")
+            uint8_t hdr[80];
+            otd_header_bytes(&wc.w.header, hdr);
+            uint32_t mid[8], tail[3];
+            header_midstate(hdr, mid, tail);
+            fold_job_consts(mid, tail[0], tail[1], tail[2], wc.target_le, &h_consts[0]);
+            h_versions[0] = wc.w.header.version;
+            if (roots_out) memcpy(roots_out, wc.w.header.merkle_root, 32);
+            return OTD_OK;
+        }
+        const uint32_t n_ver = (uint32_t)wc.n_ver;
+        const uint64_t e_first = first / wc.n_ver;
+        const uint64_t e_last = (first + n - 1) / wc.n_ver;
+        const uint32_t n_e = (uint32_t)(e_last - e_first + 1);  // <= n <= kBatch
+        const uint8_t* roots = nullptr;
+        if (wc.has_coinbase) {
+            CoinbaseDesc cd;
+            cd.blob = d_blob;
+            cd.l1 = wc.w.coinb1_len; cd.le1 = wc.w.extranonce1_len; cd.le2 = wc.w.extranonce2_size;
+            cd.l2 = wc.w.coinb2_len; cd.n_branches = wc.w.n_branches;
+            roll_extranonce2_kernel<<<(n_e + 63) / 64, 64, 0, stream>>>(
+                cd, wc.w.extranonce2_begin + e_first * wc.en2_stride, wc.en2_stride, n_e, d_roots);
+            CU_TRY(cudaGetLastError());
+            roots = d_roots;
+        }
+        instance_consts_kernel<<<(n + 63) / 64, 64, 0, stream>>>(make_template(wc), roots, (uint32_t)e_first, n_ver,
+                                                                   wc.w.version_begin, wc.ver_stride, first, n,
+                                                                   d_consts, d_versions);
+        CU_TRY(cudaGetLastError());
+        CU_TRY(cudaMemcpyAsync(h_consts, d_consts, sizeof(JobConsts) * n, cudaMemcpyDeviceToHost, stream));
+        CU_TRY(cudaMemcpyAsync(h_versions, d_versions, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, stream));
+        CU_TRY(cudaStreamSynchronize(stream));
+        if (roots_out) {
+            if (wc.has_coinbase) {
+                std::vector<uint8_t> tmp(32 * (size_t)n_e);
+                CU_TRY(cudaMemcpy(tmp.data(), d_roots, tmp.size(), cudaMemcpyDeviceToHost));
+                for (uint32_t i = 0; i < n; i++)
+                    memcpy(roots_out + 32 * (size_t)i, tmp.data() + 32 * (size_t)((first + i) / wc.n_ver - e_first), 32);
+            } else {
+                for (uint32_t i = 0; i < n; i++) memcpy(roots_out + 32 * (size_t)i, wc.w.header.merkle_root, 32);
+            }
+        }
+        return OTD_OK;
+    }
+
+    int harvest(Slot& s, const WorkCopy& wc, uint64_t seq, ShareSink& sink, RunStats& rs,
+                const std::function<bool()>& aborted, bool& abort_sent)
+    {
+        // poll instead of blocking so an abort request reaches the device promptly
+        for (;;) {
+            cudaError_t q = cudaEventQuery(s.edone);
+            if (q == cudaSuccess) break;
+            if (q != cudaErrorNotReady) return fail(OTD_ECUDA, std::string("scan kernel: ") + cudaGetErrorString(q));
+            if (!abort_sent && aborted()) {
+                CU_TRY(cudaMemcpyAsync(d_stop, &h_gen[1], sizeof(unsigned int), cudaMemcpyHostToDevice, aux));
+                abort_sent = true;
+            }
+            std::this_thread::sleep_for(std::chrono::microseconds(100));
+        }
+        float ms = 0;
+        CU_TRY(cudaEventElapsedTime(&ms, s.e0, s.e1));
+        const uint32_t pushed = s.h_hdr->count;
+        const uint32_t n = std::min(pushed, cap);
+        if (n) {
+            CU_TRY(cudaMemcpyAsync(s.h_ent, s.d_ent, sizeof(RingEntry) * (size_t)n, cudaMemcpyDeviceToHost, aux));
+            CU_TRY(cudaStreamSynchronize(aux));
+        }
+        const uint64_t hashed = std::min<uint64_t>((uint64_t)s.h_hdr->blocks_done * s.tile, s.count);
+        rs.hashes += hashed;
+        rs.launches += 1;
+        rs.candidates += s.h_hdr->candidates;
+        rs.kernel_ms += ms;
+        rs.found += pushed;
+        rs.ring_dropped += pushed - n;
+        sink.on_launch_done(hashed, s.h_hdr->candidates, ms);
+        for (uint32_t i = 0; i < n; i++) {
+            otd_share_t sh;
+            memset(&sh, 0, sizeof sh);
+            sh.channel_id = wc.w.channel_id;
+            sh.job_id = wc.w.job_id;
+            sh.nonce = s.h_ent[i].nonce;
+            sh.ntime = wc.w.header.time;
+            sh.version = s.version;
+            memcpy(sh.hash, s.h_ent[i].hash, 32);
+            sh.extranonce2 = s.en2;
+            sh.work_seq = seq;
+            sh.device_index = dev;
+            sink.on_share(sh);
+        }
+        s.busy = false;
+        return OTD_OK;
+    }
+
+    // One pass over the work's whole search space.  Returns OTD_OK also when aborted.
+    int run(const WorkCopy& wc, uint64_t seq, int variant, uint32_t launch_log2, ShareSink& sink,
+            const std::function<bool()>& aborted, RunStats& rs)
+    {
+        if (!ready) return fail(OTD_EINVAL, "engine not initialised");
+        if (variant < 0 || variant >= kNumVariants) variant = kDefaultVariant;
+        const ScanVariant& kv = kVariants[variant];
+        if (launch_log2 == 0) launch_log2 = 32;
+        launch_log2 = std::min(32u, std::max(16u, launch_log2));
+        const uint64_t chunk = 1ull << launch_log2;
+        const bool topzero = wc.target_le[7] == 0;
+        CU_TRY(cudaSetDevice(dev));
+        int rc = upload_blob(wc);
+        if (rc) return rc;
+        gen += 1;
+        if (gen == 0) gen = 1;
+        h_gen[0] = gen;
+        CU_TRY(cudaMemcpyAsync(d_stop, &h_gen[0], sizeof(unsigned int), cudaMemcpyHostToDevice, stream));
+        CU_TRY(cudaStreamSynchronize(stream));
+        bool abort_sent = false, first_launch = true, halted = false;
+        int next = 0;
+        for (uint64_t bf = 0; bf < wc.n_inst && !abort_sent && !halted; bf += kBatch) {
+            const uint32_t nb = (uint32_t)std::min<uint64_t>(kBatch, wc.n_inst - bf);
+            for (auto& s : slot)
+                if (s.busy && (rc = harvest(s, wc, seq, sink, rs, aborted, abort_sent))) return rc;
+            if (abort_sent || aborted()) break;
+            if ((rc = prepare_batch(wc, bf, nb, nullptr))) return rc;
+            for (uint32_t i = 0; i < nb && !abort_sent && !halted; i++) {
+                const uint64_t inst = bf + i;
+                const uint64_t en2 = wc.w.extranonce2_begin + (inst / wc.n_ver) * wc.en2_stride;
+                for (uint64_t off = 0; off < wc.nonce_count; off += chunk) {
+                    Slot& s = slot[next];
+                    next ^= 1;
+                    if (s.busy && (rc = harvest(s, wc, seq, sink, rs, aborted, abort_sent))) return rc;
+                    if (abort_sent || aborted()) { halted = true; break; }
+                    const uint64_t cnt = std::min(chunk, wc.nonce_count - off);
+                    CU_TRY(cudaMemsetAsync(s.d_hdr, 0, sizeof(RingHeader), stream));
+                    if (first_launch) { CU_TRY(cudaEventRecord(ev_first, stream)); first_launch = false; }
+                    CU_TRY(cudaEventRecord(s.e0, stream));
+                    cudaError_t le = kv.fn(h_consts[i], wc.w.nonce_begin + (uint32_t)off, cnt, (uint32_t)(inst & 0xffffffffu),
+                                           s.d_hdr, s.d_ent, cap, d_stop, gen, topzero, stream);
+                    if (le != cudaSuccess) return fail(OTD_ECUDA, std::string("scan launch: ") + cudaGetErrorString(le));
+                    CU_TRY(cudaEventRecord(s.e1, stream));
+                    CU_TRY(cudaEventRecord(ev_last, stream));
+                    CU_TRY(cudaMemcpyAsync(s.h_hdr, s.d_hdr, sizeof(RingHeader), cudaMemcpyDeviceToHost, stream));
+                    CU_TRY(cudaEventRecord(s.edone, stream));
+                    s.busy = true;
+                    s.count = cnt;
+                    s.tile = (uint64_t)kScanBlock * kv.v * kv.iter;
+                    s.en2 = wc.has_coinbase ? en2 : 0;
+                    s.version = h_versions[i];
+                }
+            }
+        }
+        for (int k = 0; k < 2; k++) {
+            Slot& s = slot[next];
+            next ^= 1;
+            if (s.busy && (rc = harvest(s, wc, seq, sink, rs, aborted, abort_sent))) return rc;
+        }
+        if (!first_launch) {
+            float span = 0;
+            CU_TRY(cudaEventSynchronize(ev_last));
+            CU_TRY(cudaEventElapsedTime(&span, ev_first, ev_last));
+            rs.span_ms += span;
+        }
+        return OTD_OK;
+    }
+};
+
+// --------------------------------------------------------- synchronous scan --
+struct CollectSink : ShareSink {
+    std::vector<otd_share_t> shares;
+    void on_share(const otd_share_t& s) override { shares.push_back(s); }
+    void on_launch_done(uint64_t, uint64_t, double) override {}
+};
+
+static std::mutex g_pool_mu;
+static std::vector<std::unique_ptr<Engine>> g_pool;       // one cached engine per device
+static std::vector<std::unique_ptr<std::mutex>> g_pool_locks;
+
+static int pool_engine(int dev, Engine** out, std::mutex** lock)
+{
+    int rc = check_device(dev);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> g(g_pool_mu);
+    if ((int)g_pool.size() <= dev) {
+        g_pool.resize(dev + 1);
+        while ((int)g_pool_locks.size() <= dev) g_pool_locks.emplace_back(new std::mutex());
+    }
+    if (!g_pool[dev]) {
+        std::unique_ptr<Engine> e(new Engine());
+        rc = e->init(dev, 1u << 16);
+        if (rc) return rc;
+        g_pool[dev] = std::move(e);
+    }
+    *out = g_pool[dev].get();
+    *lock = g_pool_locks[dev].get();
+    return OTD_OK;
+}
+
+extern "C" int otd_scan(int device_index, const otd_work_t* work, int kernel_variant, otd_share_t* out,
+                        uint32_t max_shares, uint64_t* n_found, uint64_t* hashes, double* device_ms,
+                        uint64_t* launches)
+{
+    WorkCopy wc;
+    int rc = copy_work(work, &wc);
+    if (rc) return rc;
+    if (max_shares && !out) return fail(OTD_EINVAL, "otd_scan: out is NULL");
+    Engine* eng;
+    std::mutex* lock;
+    if ((rc = pool_engine(device_index, &eng, &lock))) return rc;
+    std::lock_guard<std::mutex> g(*lock);
+    CollectSink sink;
+    RunStats rs;
+    rc = eng->run(wc, 1, kernel_variant, 32, sink, [] { return false; }, rs);
+    if (rc) return rc;
+    std::sort(sink.shares.begin(), sink.shares.end(), [](const otd_share_t& a, const otd_share_t& b) {
+        if (a.extranonce2 != b.extranonce2) return a.extranonce2 < b.extranonce2;
+        if (a.version != b.version) return a.version < b.version;
+        return a.nonce < b.nonce;
+    });
+    const size_t n = std::min<size_t>(sink.shares.size(), max_shares);
+    for (size_t i = 0; i < n; i++) out[i] = sink.shares[i];
+    if (n_found) *n_found = rs.found;
+    if (hashes) *hashes = rs.hashes;
+    if (device_ms) *device_ms = rs.span_ms;
+    if (launches) *launches = rs.launches;
+    return OTD_OK;
+}
+
+extern "C" int otd_prepare_instances(int device_index, const otd_work_t* work, uint32_t first, uint32_t n,
+                                     uint8_t* merkle_roots, uint32_t* versions, uint64_t* extranonce2s,
+                                     uint8_t* midstates)
+{
+    WorkCopy wc;
+    int rc = copy_work(work, &wc);
+    if (rc) return rc;
+    if ((uint64_t)first + n > wc.n_inst) return fail(OTD_EINVAL, "instance range outside the work's search space");
+    Engine* eng;
+    std::mutex* lock;
+    if ((rc = pool_engine(device_index, &eng, &lock))) return rc;
+    std::lock_guard<std::mutex> g(*lock);
+    CU_TRY(cudaSetDevice(device_index));
+    if ((rc = eng->upload_blob(wc))) return rc;
+    for (uint32_t done = 0; done < n; done += Engine::kBatch) {
+        const uint32_t nb = std::min<uint32_t>(Engine::kBatch, n - done);
+        rc = eng->prepare_batch(wc, (uint64_t)first + done, nb, merkle_roots ? merkle_roots + 32ull * done : nullptr);
+        if (rc) return rc;
+        for (uint32_t i = 0; i < nb; i++) {
+            const uint64_t inst = (uint64_t)first + done + i;
+            if (versions) versions[done + i] = eng->h_versions[i];
+            if (extranonce2s) extranonce2s[done + i] = wc.has_coinbase ? wc.w.extranonce2_begin + (inst / wc.n_ver) * wc.en2_stride : 0;
+            if (midstates)
+                for (int k = 0; k < 8; k++) {
+                    const uint32_t v = eng->h_consts[i].mid[k];
+                    uint8_t* p = midstates + 32ull * (done + i) + 4 * k;
+                    p[0] = v >> 24; p[1] = v >> 16; p[2] = v >> 8; p[3] = v;
+                }
+        }
+    }
+    return OTD_OK;
+}
+
+// ------------------------------------------------------------ hash_headers --
+extern "C" int otd_hash_headers(int device_index, const uint8_t* headers80, size_t n, uint8_t* hashes32)
+{
+    int rc = check_device(device_index);
+    if (rc) return rc;
+    if (n == 0) return OTD_OK;
+    if (!headers80 || !hashes32) return fail(OTD_EINVAL, "otd_hash_headers: NULL buffer");
+    CU_TRY(cudaSetDevice(device_index));
+    uint8_t *d_in = nullptr, *d_out = nullptr;
+    CU_TRY(cudaMalloc(&d_in, 80 * n));
+    cudaError_t e = cudaMalloc(&d_out, 32 * n);
+    if (e != cudaSuccess) { cudaFree(d_in); return fail(OTD_ENOMEM, cudaGetErrorString(e)); }
+    e = cudaMemcpy(d_in, headers80, 80 * n, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        hash_headers_kernel<<<(unsigned)((n + 127) / 128), 128>>>(d_in, n, d_out);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(hashes32, d_out, 32 * n, cudaMemcpyDeviceToHost);
+    cudaFree(d_in);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return fail(OTD_ECUDA, std::string("otd_hash_headers: ") + cudaGetErrorString(e));
+    return OTD_OK;
+}
+
+// ------------------------------------------------------------------ worker --
+struct otd_worker : ShareSink {
+    int dev = -1;
+    otd_worker_config_t cfg;
+    Engine eng;
+    std::thread th;
+    std::mutex mu;
+    std::condition_variable cv_work, cv_share;
+    std::shared_ptr<WorkCopy> work;
+    std::atomic<uint64_t> seq{0};
+    std::atomic<bool> stop{false};
+    bool exhausted = false;
+    std::deque<otd_share_t> queue;
+    std::atomic<uint64_t> hashes{0}, shares{0}, dropped{0}, launches{0}, candidates{0};
+    double device_ms = 0;
+    std::chrono::steady_clock::time_point t_start;
+    std::string thread_error;
+
+    void on_share(const otd_share_t& s) override
+    {
+        shares.fetch_add(1);
+        std::lock_guard<std::mutex> g(mu);
+        if (queue.size() >= cfg.queue_capacity) {
+            dropped.fetch_add(1);  // non-blocking send, like worker.go:271-275
+            return;
+        }
+        queue.push_back(s);
+        cv_share.notify_all();
+    }
+    void on_launch_done(uint64_t h, uint64_t c, double ms) override
+    {
+        hashes.fetch_add(h);
+        launches.fetch_add(1);
+        candidates.fetch_add(c);
+        std::lock_guard<std::mutex> g(mu);
+        device_ms += ms;
+    }
+
+    void main_loop()
+    {
+        cudaSetDevice(dev);
+        for (;;) {
+            std::shared_ptr<WorkCopy> wc;
+            uint64_t my_seq;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv_work.wait(lk, [&] { return stop.load() || (work && !exhausted); });
+                if (stop.load()) return;
+                wc = work;
+                my_seq = seq.load();
+            }
+            RunStats rs;
+            int rc = eng.run(*wc, my_seq, cfg.kernel_variant, cfg.launch_log2, *this,
+                             [&] { return stop.load() || seq.load() != my_seq; }, rs);
+            shares.fetch_add(rs.ring_dropped);  // found on the device, lost to a full ring
+            dropped.fetch_add(rs.ring_dropped);
+            std::lock_guard<std::mutex> g(mu);
+            if (rc) {
+                thread_error = otd_last_error();
+                exhausted = true;  // surfaces as a zero hash rate, like a wedged device
+                cv_share.notify_all();
+                continue;
+            }
+            if (!stop.load() && seq.load() == my_seq && !(wc->w.flags & OTD_WORK_REPEAT)) {
+                exhausted = true;
+                cv_share.notify_all();
+            }
+        }
+    }
+};
+
+extern "C" otd_worker_t* otd_worker_create(int device_index, const otd_worker_config_t* cfg)
+{
+    std::unique_ptr<otd_worker> w(new otd_worker());
+    w->dev = device_index;
+    otd_worker_config_t c;
+    memset(&c, 0, sizeof c);
+    c.kernel_variant = -1;
+    if (cfg) c = *cfg;
+    if (c.ring_capacity == 0) c.ring_capacity = 4096;
+    if (c.queue_capacity == 0) c.queue_capacity = 65536;
+    if (c.launch_log2 == 0) c.launch_log2 = 32;
+    if (c.launch_log2 < 16 || c.launch_log2 > 32) {
+        fail(OTD_EINVAL, "launch_log2 must be in [16, 32]");
+        return nullptr;
+    }
+    w->cfg = c;
+    if (w->eng.init(device_index, c.ring_capacity) != OTD_OK) {
+        w->eng.destroy();
+        return nullptr;
+    }
+    w->t_start = std::chrono::steady_clock::now();
+    otd_worker* raw = w.release();
+    raw->th = std::thread([raw] { raw->main_loop(); });
+    return raw;
+}
+
+extern "C" int64_t otd_worker_set_work(otd_worker_t* w, const otd_work_t* work)
+{
+    if (!w) return fail(OTD_EINVAL, "worker is NULL");
+    std::shared_ptr<WorkCopy> wc;
+    if (work) {
+        wc = std::make_shared<WorkCopy>();
+        int rc = copy_work(work, wc.get());
+        if (rc) return rc;
+    }
+    std::lock_guard<std::mutex> g(w->mu);
+    w->work = wc;
+    w->exhausted = false;
+    const uint64_t s = w->seq.fetch_add(1) + 1;
+    w->cv_work.notify_all();
+    w->cv_share.notify_all();
+    return (int64_t)s;
+}
+
+extern "C" int otd_worker_poll_shares(otd_worker_t* w, otd_share_t* out, int max_shares, int timeout_ms)
+{
+    if (!w || !out || max_shares <= 0) return fail(OTD_EINVAL, "otd_worker_poll_shares: bad argument");
+    std::unique_lock<std::mutex> lk(w->mu);
+    auto ready = [&] { return !w->queue.empty() || w->exhausted || w->stop.load(); };
+    if (timeout_ms < 0) w->cv_share.wait(lk, ready);
+    else if (timeout_ms > 0) w->cv_share.wait_for(lk, std::chrono::milliseconds(timeout_ms), ready);
+    int n = 0;
+    while (n < max_shares && !w->queue.empty()) {
+        out[n++] = w->queue.front();
+        w->queue.pop_front();
+    }
+    if (n == 0 && !w->thread_error.empty()) return fail(OTD_ECUDA, w->thread_error);
+    return n;
+}
+
+extern "C" int otd_worker_wait_exhausted(otd_worker_t* w, int timeout_ms)
+{
+    if (!w) return fail(OTD_EINVAL, "worker is NULL");
+    std::unique_lock<std::mutex> lk(w->mu);
+    auto done = [&] { return w->exhausted || w->stop.load(); };
+    if (timeout_ms < 0) w->cv_share.wait(lk, done);
+    else w->cv_share.wait_for(lk, std::chrono::milliseconds(timeout_ms), done);
+    if (!w->thread_error.empty()) return fail(OTD_ECUDA, w->thread_error);
+    return w->exhausted ? 1 : 0;
+}
+
+extern "C" int otd_worker_stats(otd_worker_t* w, otd_stats_t* out)
+{
+    if (!w || !out) return fail(OTD_EINVAL, "otd_worker_stats: bad argument");
+    memset(out, 0, sizeof *out);
+    const auto now = std::chrono::steady_clock::now();
+    out->uptime_ns = (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(now - w->t_start).count();
+    out->hashes_total = w->hashes.load();
+    out->shares_found = w->shares.load();
+    out->shares_dropped = w->dropped.load();
+    out->launches = w->launches.load();
+    out->candidates = w->candidates.load();
+    out->hash_rate = out->uptime_ns ? (double)out->hashes_total / ((double)out->uptime_ns * 1e-9) : 0.0;
+    out->work_seq = w->seq.load();
+    std::lock_guard<std::mutex> g(w->mu);
+    out->device_ms = w->device_ms;
+    out->has_work = w->work ? 1 : 0;
+    out->exhausted = w->exhausted ? 1 : 0;
+    return OTD_OK;
+}
+
+extern "C" int otd_worker_has_work(otd_worker_t* w)
+{
+    if (!w) return fail(OTD_EINVAL, "worker is NULL");
+    std::lock_guard<std::mutex> g(w->mu);
+    return w->work ? 1 : 0;
+}
+extern "C" int otd_worker_device_index(otd_worker_t* w) { return w ? w->dev : fail(OTD_EINVAL, "worker is NULL"); }
+
+extern "C" int otd_worker_destroy(otd_worker_t* w)
+{
+    if (!w) return OTD_OK;
+    {
+        std::lock_guard<std::mutex> g(w->mu);
+        w->stop.store(true);
+        w->cv_work.notify_all();
+        w->cv_share.notify_all();
+    }
+    if (w->th.joinable()) w->th.join();
+    w->eng.destroy();
+    delete w;
+    return OTD_OK;
+}
+
+// ---------------------------------------------------------------- int peak --
+static const char* kIntPeakNames[IPM_COUNT] = {"lop3", "shf", "iadd3", "imad", "mix_alu",
+                                               "mix_dual", "mix_dual1", "imad_wide", "prmt", "alu_fma"};
+
+extern "C" int otd_int_peak_modes(char (*names)[32], int max_names)
+{
+    if (names)
+        for (int i = 0; i < IPM_COUNT && i < max_names; i++) snprintf(names[i], 32, "%s", kIntPeakNames[i]);
+    return IPM_COUNT;
+}
+
+template <int MODE>
+static cudaError_t launch_peak(int grid, int iters, uint32_t* sink, long long* cyc, cudaStream_t st)
+{
+    int_peak_kernel<MODE><<<grid, 256, 0, st>>>(iters, 1u, 12345u, sink, cyc);
+    return cudaGetLastError();
+}
+
+extern "C" int otd_int_peak(int device_index, int mode, int iters, double* ops_per_s, double* sm_mhz, double* ms_out)
+{
+    int rc = check_device(device_index);
+    if (rc) return rc;
+    if (mode < 0 || mode >= IPM_COUNT) return fail(OTD_EINVAL, "otd_int_peak: unknown mode");
+    if (iters <= 0) iters = 2048;
+    CU_TRY(cudaSetDevice(device_index));
+    int sms = 0;
+    CU_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_index));
+    const int blocks_per_sm = 4;  // 1024 threads/SM = 8 warps per scheduler
+    const int grid = sms * blocks_per_sm;
+    uint32_t* d_sink = nullptr;
+    long long* d_cyc = nullptr;
+    CU_TRY(cudaMalloc(&d_sink, sizeof(uint32_t)));
+    CU_TRY(cudaMalloc(&d_cyc, sizeof(long long)));
+    cudaStream_t st;
+    CU_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    cudaEvent_t e0, e1;
+    CU_TRY(cudaEventCreate(&e0));
+    CU_TRY(cudaEventCreate(&e1));
+    typedef cudaError_t (*fn_t)(int, int, uint32_t*, long long*, cudaStream_t);
+    static const fn_t fns[IPM_COUNT] = {launch_peak<0>, launch_peak<1>, launch_peak<2>, launch_peak<3>, launch_peak<4>,
+                                        launch_peak<5>, launch_peak<6>, launch_peak<7>, launch_peak<8>, launch_peak<9>};
+    cudaError_t e = cudaSuccess;
+    for (int w = 0; w < 2 && e == cudaSuccess; w++) e = fns[mode](grid, iters / 4 + 1, d_sink, d_cyc, st);  // warm-up
+    float ms = 0;
+    long long cyc = 0;
+    if (e == cudaSuccess) e = cudaEventRecord(e0, st);
+    if (e == cudaSuccess) e = fns[mode](grid, iters, d_sink, d_cyc, st);
+    if (e == cudaSuccess) e = cudaEventRecord(e1, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
+    if (e == cudaSuccess) e = cudaMemcpy(&cyc, d_cyc, sizeof cyc, cudaMemcpyDeviceToHost);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st); cudaFree(d_sink); cudaFree(d_cyc);
+    if (e != cudaSuccess) return fail(OTD_ECUDA, std::string("otd_int_peak: ") + cudaGetErrorString(e));
+    const double ops = (double)grid * 256.0 * (double)iters * kIpUnroll * kIpChains * ip_ops_per_step(mode);
+    if (ops_per_s) *ops_per_s = ops / (ms * 1e-3);
+    if (sm_mhz) *sm_mhz = (double)cyc / (ms * 1e-3) / 1e6;
+    if (ms_out) *ms_out = ms;
+    return OTD_OK;
+}

@@ -1,0 +1,70 @@
+"""The product's folded scan arithmetic (otedama_b200/csrc/scan_core.cuh,
+sha256_core.cuh) instantiated for the HOST and compared with the oracle, so the
+constant folding and round bookkeeping are checked on a CPU-only box.  The host
+build is a test helper (tests/_hostcheck/fold_check.cpp), not a product path."""
+import ctypes
+import os
+import random
+import struct
+import subprocess
+
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+IV7 = 0x5BE0CD19
+
+
+@pytest.fixture(scope="module")
+def fold():
+    src = os.path.join(HERE, "_hostcheck", "fold_check.cpp")
+    so = os.path.join(HERE, "_hostcheck", "libfoldcheck.so")
+    deps = [src] + [os.path.join(HERE, "..", "otedama_b200", "csrc", f) for f in ("scan_core.cuh", "sha256_core.cuh")]
+    if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
+        subprocess.check_call(["g++", "-O1", "-std=c++17", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-o", so, src])
+    L = ctypes.CDLL(so)
+    L.fc_iv7.restype = ctypes.c_uint32
+    return L
+
+
+def _e60(L, h76, nonces):
+    v = len(nonces)
+    arr = (ctypes.c_uint32 * v)(*nonces)
+    out = (ctypes.c_uint32 * v)()
+    assert L.fc_scan_e60(h76, arr, v, out) == 0
+    return list(out)
+
+
+def test_top_word_matches_oracle(fold, oracle):
+    assert fold.fc_iv7() == IV7
+    rnd = random.Random(1)
+    genesis = bytes.fromhex("0100000000000000000000000000000000000000000000000000000000000000000000003ba3edfd7a7b12b27ac72c3e67768f617fc81bc3888a51323a9fb8aa4b1e5e4a29ab5f49ffff001d")
+    cases = [(genesis, [2083236893])]
+    for _ in range(200):
+        v = rnd.choice([1, 2, 4])
+        cases.append((rnd.randbytes(76), [rnd.getrandbits(32) for _ in range(v)]))
+    cases.append((b"\x00" * 76, [0, 0xFFFFFFFF]))
+    cases.append((b"\xff" * 76, [0xFFFFFFFF, 1, 2, 3]))
+    for h76, nonces in cases:
+        for n, e in zip(nonces, _e60(fold, h76, nonces)):
+            d = oracle.sha256d(h76 + struct.pack("<I", n))
+            h7 = struct.unpack(">I", d[28:32])[0]
+            assert (e + IV7) & 0xFFFFFFFF == h7
+    # the genesis nonce is exactly the "top word zero" constant the kernel tests for
+    assert _e60(fold, genesis, [2083236893])[0] == (-IV7) & 0xFFFFFFFF
+
+
+def test_midstate_digest_and_compare(fold, oracle):
+    rnd = random.Random(2)
+    out = ctypes.create_string_buffer(32)
+    le = ctypes.c_int()
+    for _ in range(200):
+        h76, n = rnd.randbytes(76), rnd.getrandbits(32)
+        want = oracle.sha256d(h76 + struct.pack("<I", n))
+        # targets around the hash itself exercise every branch of the 256-bit compare
+        hv = int.from_bytes(want, "little")
+        for tv in (hv, hv - 1, hv + 1, hv ^ (1 << rnd.randrange(256)), rnd.getrandbits(256)):
+            tv = max(0, min(tv, (1 << 256) - 1))
+            t = tv.to_bytes(32, "little")
+            fold.fc_sha256d_mid(h76, n, t, out, ctypes.byref(le))
+            assert out.raw == want
+            assert bool(le.value) == oracle.less_or_equal(want, t) == (hv <= tv)

@@ -1,0 +1,414 @@
+"""Parity tests proper: the CUDA path, called through the C ABI, against the CPU
+oracle on the same seeded inputs.  Bit-exact (integer work): share sets must be
+identical — nonce, hash, ntime, version, extranonce2."""
+import hashlib
+import os
+import random
+import struct
+import time
+
+import pytest
+
+from otedama_b200 import workloads as W
+
+pytestmark = pytest.mark.gpu
+
+NCPU = os.cpu_count() or 1
+
+
+@pytest.fixture(scope="module")
+def miner(product):
+    from otedama_b200 import capi, miner as m
+    if capi.lib().otd_device_count() <= 0:
+        pytest.fail("no CUDA device: the gpu-marked tests must run on the B200 box")
+    return m
+
+
+def mheader(m, f):
+    return m.Header(f["version"], f["prev_hash"], f["merkle_root"], f["time"], f["bits"], 0)
+
+
+def oheader(o, f, version=None, merkle_root=None):
+    return o.Header(f["version"] if version is None else version, f["prev_hash"],
+                    f["merkle_root"] if merkle_root is None else merkle_root, f["time"], f["bits"], 0)
+
+
+def key(shares):
+    return sorted((s.extranonce2, s.version, s.nonce, s.hash, s.ntime) for s in shares)
+
+
+def okey(shares, extranonce2=0):
+    return sorted((extranonce2, s.version, s.nonce, s.hash, s.ntime) for s in shares)
+
+
+# ---------------------------------------------------------------- HashHeader --
+def test_device_enumeration(miner):
+    from otedama_b200 import hal
+    devs = hal.CudaDriver().enumerate()
+    assert devs
+    ident = devs[0].identity()
+    ident.validate()
+    assert ident.id == "gpu-cuda0" and ident.family == "gpu" and ident.vendor == "nvidia"
+    caps = devs[0].capabilities()
+    assert caps.sha256d and caps.general_compute  # unlike the sysfs driver (gpu_linux_test.go:152-174)
+    assert devs[0].info.sm_count >= 100 and devs[0].info.cc_major == 10
+    devs[0].shutdown(); devs[0].shutdown()
+
+
+@pytest.mark.parametrize("n", [1, 2, 127, 128, 129, 5000])
+def test_hash_headers_matches_oracle(miner, oracle, n):
+    rnd = random.Random(n)
+    hdrs = [rnd.randbytes(80) for _ in range(n)]
+    hdrs[0] = bytes.fromhex(W.GENESIS_HEADER_HEX)
+    got = miner.hash_headers(hdrs)
+    want = oracle.hash_headers(b"".join(hdrs))
+    assert b"".join(got) == want
+    assert got[0].hex() == W.GENESIS_HASH_HEX
+    assert miner.hash_headers([]) == []
+
+
+def test_hash_header_single(miner, oracle):
+    h = miner.parse_header(bytes.fromhex(W.GENESIS_HEADER_HEX))
+    assert miner.hash_header(h).hex() == W.GENESIS_HASH_HEX
+
+
+# ----------------------------------------------------------------- K1: scan --
+def variants(miner):
+    return list(range(len(miner.scan_variants())))
+
+
+def test_genesis_window_every_variant(miner, oracle):
+    f = W.genesis_fields()
+    t = miner.target_from_nbits(W.DIFF1_NBITS)
+    for v in variants(miner):
+        r = miner.scan(miner.Work(job_id=7, channel_id=3, header=mheader(miner, f), nbits=W.DIFF1_NBITS, target=t,
+                                  nonce_begin=W.GENESIS_NONCE - (1 << 23), nonce_count=1 << 24), variant=v)
+        assert r.hashes == 1 << 24 and r.found == 1
+        s = r.shares[0]
+        assert (s.nonce, s.hash.hex()) == (W.GENESIS_NONCE, W.GENESIS_HASH_HEX)
+        assert (s.job_id, s.channel_id, s.ntime, s.version, s.device_id) == (7, 3, f["time"], f["version"], "gpu-cuda0")
+
+
+def test_equality_counts_as_a_share(miner):
+    """Hash.LessOrEqual returns true on equality (sha256d.go:102)."""
+    f = W.genesis_fields()
+    hv = int.from_bytes(bytes.fromhex(W.GENESIS_HASH_HEX), "little")
+    for tv, want in ((hv, 1), (hv - 1, 0), (hv + 1, 1)):
+        r = miner.scan(miner.Work(header=mheader(miner, f), target=tv.to_bytes(32, "little"),
+                                  nonce_begin=W.GENESIS_NONCE - 1000, nonce_count=2000))
+        assert r.found == want
+
+
+def test_dense_windows_match_golden_and_oracle(miner, oracle, golden):
+    for case in golden["synthetic_windows"]["cases"]:
+        f = W.config2_fields(case["index"])
+        t = bytes.fromhex(case["target_hex"])
+        for v in variants(miner):
+            r = miner.scan(miner.Work(header=mheader(miner, f), target=t, nonce_begin=case["first"],
+                                      nonce_count=case["count"]), variant=v)
+            assert [s.nonce for s in r.shares] == case["nonces"]
+            assert hashlib.sha256(b"".join(s.hash for s in r.shares)).hexdigest() == case["hash_digest"]
+            assert r.hashes == case["count"] and r.found == len(case["nonces"])
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_random_headers_random_targets(miner, oracle, seed):
+    rnd = random.Random(seed)
+    for _ in range(6):
+        f = {"version": rnd.getrandbits(32), "prev_hash": rnd.randbytes(32), "merkle_root": rnd.randbytes(32),
+             "time": rnd.getrandbits(32), "bits": rnd.getrandbits(32)}
+        # targets from "every hash" down to ~2^-20, in both kernel specialisations' ranges
+        t = (rnd.getrandbits(256) >> rnd.choice([0, 1, 8, 12, 16, 20])).to_bytes(32, "little")
+        first = rnd.choice([0, rnd.getrandbits(32) & ~0xFFFFF, (1 << 32) - (1 << 18)])
+        count = rnd.choice([1, 255, 4097, 100003, 1 << 18])
+        count = min(count, (1 << 32) - first)
+        want, _, _ = oracle.grind(oheader(oracle, f), t, first, count, threads=NCPU)
+        r = miner.scan(miner.Work(header=mheader(miner, f), target=t, nonce_begin=first, nonce_count=count),
+                       variant=rnd.randrange(len(miner.scan_variants())), max_shares=1 << 18)
+        assert r.hashes == count
+        assert key(r.shares) == okey(want)
+
+
+def test_all_ff_target_overflows_the_ring_without_hanging(miner):
+    """integration_test.go:129-132 uses an all-0xFF target: every nonce is a share.
+    The device ring is bounded; the excess is counted, never blocks."""
+    f = W.config2_fields(5)
+    r = miner.scan(miner.Work(header=mheader(miner, f), target=b"\xff" * 32, nonce_count=1 << 20), max_shares=1 << 17)
+    assert r.found == 1 << 20 and r.hashes == 1 << 20
+    assert len(r.shares) == 1 << 16  # ring capacity of the synchronous engine
+    assert len({s.nonce for s in r.shares}) == len(r.shares)
+
+
+def test_full_nonce_range_genesis(miner, golden):
+    """configs[0]: full 2^32 scan must find exactly nonce 2083236893 — the same
+    set the CPU oracle's full scan produced (tests/golden/genesis_full_scan.json)."""
+    f = W.genesis_fields()
+    r = miner.scan(miner.Work(header=mheader(miner, f), nbits=W.DIFF1_NBITS,
+                              target=miner.target_from_nbits(W.DIFF1_NBITS)))
+    assert r.hashes == 1 << 32
+    assert [(s.nonce, s.hash.hex()) for s in r.shares] == [(W.GENESIS_NONCE, W.GENESIS_HASH_HEX)]
+    g = golden.get("genesis_full_scan")
+    if g:
+        assert [(s.nonce, s.hash.hex()) for s in r.shares] == [(x["nonce"], x["hash"]) for x in g["shares"]]
+
+
+def test_config2_headers_full_range_soundness(miner, oracle):
+    """configs[1] (subset): full nonce range at difficulty 1 on synthetic headers.
+    Soundness bit-exact: every share re-hashed by the oracle meets the target."""
+    t = miner.target_from_difficulty(1.0)
+    total = 0
+    for i in (1, 2, 3, 4):
+        f = W.config2_fields(i)
+        r = miner.scan(miner.Work(header=mheader(miner, f), target=t))
+        assert r.hashes == 1 << 32
+        for s in r.shares:
+            oh = oheader(oracle, f)
+            oh.nonce = s.nonce
+            assert oracle.hash_header(oh) == s.hash and oracle.less_or_equal(s.hash, t)
+        total += r.found
+    assert total <= 20  # Poisson mean 4
+
+
+# ------------------------------------------------- K2: BIP-320 version roll --
+def test_version_rolling_matches_oracle(miner, oracle):
+    from tests import pysha
+    c4 = W.config4_v2()
+    f = dict(c4)
+    t = oracle.target_from_difficulty(2.0 ** -18)
+    work = miner.Work(job_id=9, header=mheader(miner, f), target=t, version_mask=c4["mask"], version_begin=3,
+                      version_count=40, version_stride=5, nonce_begin=0x10000000, nonce_count=1 << 16)
+    inst = miner.prepare_instances(work, 0, 40)
+    want = []
+    for i in range(40):
+        ver = oracle.bip320_version(c4["version"], c4["mask"], 3 + 5 * i)
+        assert inst[i].version == ver and inst[i].merkle_root == c4["merkle_root"]
+        oh = oheader(oracle, f, version=ver)
+        assert inst[i].midstate == pysha.midstate(oh.bytes())
+        sh, _, _ = oracle.grind(oh, t, 0x10000000, 1 << 16, threads=NCPU)
+        want += okey(sh)
+    r = miner.scan(work)
+    assert r.hashes == 40 << 16 and r.launches == 40
+    assert key(r.shares) == sorted(want) and len(want) > 100
+    assert all(s.job_id == 9 for s in r.shares)
+
+
+def test_version_rolling_default_count_covers_the_mask(miner, oracle):
+    # a 3-bit mask: 8 versions, stride 3 from 1 -> k = 1, 4, 7
+    f = W.config2_fields(9)
+    t = oracle.target_from_difficulty(2.0 ** -20)
+    r = miner.scan(miner.Work(header=mheader(miner, f), target=t, version_mask=0x0000E000, version_begin=1,
+                              version_stride=3, nonce_count=1 << 14))
+    assert r.launches == 3
+    want = []
+    for k in (1, 4, 7):
+        ver = oracle.bip320_version(f["version"], 0xE000, k)
+        sh, _, _ = oracle.grind(oheader(oracle, f, version=ver), t, 0, 1 << 14)
+        want += okey(sh)
+    assert key(r.shares) == sorted(want)
+
+
+# --------------------------------------- K3: extranonce2 roll + merkle root --
+def v1_work(miner, c3, **kw):
+    f = {"version": c3["version"], "prev_hash": c3["prev_hash"], "merkle_root": b"\x00" * 32,
+         "time": c3["time"], "bits": c3["bits"]}
+    return miner.Work(header=mheader(miner, f), coinb1=c3["coinb1"], extranonce1=c3["extranonce1"],
+                      coinb2=c3["coinb2"], merkle_branches=c3["branches"],
+                      extranonce2_size=c3["extranonce2_size"], **kw), f
+
+
+def test_extranonce2_roll_and_merkle_root(miner, oracle, golden):
+    c3 = W.config3_v1()
+    work, f = v1_work(miner, c3, target=b"\xff" * 32, extranonce2_begin=0, extranonce2_count=8)
+    inst = miner.prepare_instances(work, 0, 8)
+    assert [i.merkle_root.hex() for i in inst] == golden["synthetic_windows"]["config3_roots_e0_7"]
+    assert [i.extranonce2 for i in inst] == list(range(8))
+    # the genesis coinbase split as coinb1|en1|en2|coinb2 reproduces the genesis merkle root
+    g = golden["reference_vectors"]["genesis_coinbase_tx"]
+    tx = bytes.fromhex(g["tx_hex"])
+    en2 = int.from_bytes(tx[54:58], "little")
+    gw = miner.Work(target=b"\xff" * 32, coinb1=tx[:50], extranonce1=tx[50:54], coinb2=tx[58:], extranonce2_size=4,
+                    extranonce2_begin=en2, extranonce2_count=1)
+    assert miner.prepare_instances(gw, 0, 1)[0].merkle_root.hex() == g["merkle_root_hex"]
+
+
+@pytest.mark.parametrize("l1,l2,size,nb", [(1, 0, 1, 0), (41, 9, 4, 1), (42, 9, 4, 2), (50, 9, 4, 3), (51, 9, 4, 0),
+                                           (58, 107, 8, 12), (120, 200, 8, 5), (0, 300, 2, 1), (500, 700, 16, 4)])
+def test_coinbase_lengths_and_padding_edges(miner, oracle, l1, l2, size, nb):
+    """Coinbase lengths straddling the 55/56/64-byte padding boundaries, 0..12 branches."""
+    rnd = random.Random(l1 * 1000 + l2)
+    cb1, en1, cb2 = rnd.randbytes(l1), rnd.randbytes(4), rnd.randbytes(l2)
+    br = [rnd.randbytes(32) for _ in range(nb)]
+    begin = 0 if size < 2 else 250
+    work = miner.Work(target=b"\xff" * 32, coinb1=cb1, extranonce1=en1, coinb2=cb2, merkle_branches=br,
+                      extranonce2_size=size, extranonce2_begin=begin, extranonce2_count=12, extranonce2_stride=1)
+    inst = miner.prepare_instances(work, 0, 12)
+    for i, it in enumerate(inst):
+        e = begin + i
+        want = oracle.v1_merkle_root(cb1, en1, oracle.extranonce2_bytes(e, size), cb2, br)
+        assert it.merkle_root == want and it.extranonce2 == e
+
+
+def test_v1_scan_with_extranonce2_matches_oracle(miner, oracle):
+    c3 = W.config3_v1()
+    t = oracle.target_from_difficulty(2.0 ** -17)
+    work, f = v1_work(miner, c3, job_id=60, target=t, extranonce2_begin=5, extranonce2_count=20,
+                      extranonce2_stride=3, nonce_begin=0xFFFF0000, nonce_count=1 << 16)
+    r = miner.scan(work)
+    want = []
+    for i in range(20):
+        e = 5 + 3 * i
+        root = oracle.v1_merkle_root(c3["coinb1"], c3["extranonce1"], oracle.extranonce2_bytes(e, 8), c3["coinb2"],
+                                     c3["branches"])
+        sh, _, _ = oracle.grind(oheader(oracle, f, merkle_root=root), t, 0xFFFF0000, 1 << 16, threads=NCPU)
+        want += okey(sh, extranonce2=e)
+    assert key(r.shares) == sorted(want) and len(want) > 100
+    assert r.hashes == 20 << 16
+
+
+def test_extranonce2_times_version_space(miner, oracle):
+    """nonce x extranonce2 x BIP-320 version bits, more instances than one preparation batch."""
+    c3 = W.config3_v1()
+    t = oracle.target_from_difficulty(2.0 ** -22)
+    work, f = v1_work(miner, c3, target=t, extranonce2_begin=1, extranonce2_count=30, version_mask=W.BIP320_MASK,
+                      version_begin=0, version_count=10, nonce_count=1 << 12)
+    r = miner.scan(work)
+    assert r.launches == 300 and r.hashes == 300 << 12
+    want = []
+    for e in range(1, 31):
+        root = oracle.v1_merkle_root(c3["coinb1"], c3["extranonce1"], oracle.extranonce2_bytes(e, 8), c3["coinb2"],
+                                     c3["branches"])
+        for k in range(10):
+            ver = oracle.bip320_version(c3["version"], W.BIP320_MASK, k)
+            sh, _, _ = oracle.grind(oheader(oracle, f, version=ver, merkle_root=root), t, 0, 1 << 12)
+            want += okey(sh, extranonce2=e)
+    assert key(r.shares) == sorted(want) and len(want) > 50
+
+
+# ------------------------------------------------------------------- Worker --
+def easy_work(miner, job_id=1, i=11, **kw):
+    f = W.config2_fields(i)
+    return miner.Work(job_id=job_id, channel_id=2, header=mheader(miner, f), nbits=f["bits"],
+                      target=kw.pop("target", b"\xff" * 32), **kw), f
+
+
+def test_worker_start_twice_raises_and_stop_is_idempotent(miner):
+    w = miner.Worker().start()          # TestWorker_StartTwicePanics (worker_test.go:56-69)
+    with pytest.raises(RuntimeError):
+        w.start()
+    w.stop(); w.stop()                  # TestWorker_StartAndStop (worker_test.go:71-91)
+
+
+def test_worker_idle_until_set_work_then_finds_shares(miner, oracle):
+    with miner.Worker(miner.WorkerConfig(launch_log2=16)) as w:
+        assert not w.has_work()
+        time.sleep(0.05)
+        assert w.stats().hashes_total == 0
+        work, f = easy_work(miner, job_id=42, nonce_count=1 << 16)
+        w.set_work(work)                # TestWorker_FindsSharesWithEasyTarget (worker_test.go:93-140)
+        assert w.has_work()
+        assert w.wait_exhausted(10000)
+        shares = []
+        while True:
+            got = w.poll_shares(4096, 0)
+            if not got:
+                break
+            shares += got
+        st = w.stats()
+        assert st.exhausted and st.hashes_total == 1 << 16 and st.shares_found == 1 << 16
+        assert st.shares_dropped == st.shares_found - len(shares)
+        assert st.hash_rate > 0 and st.uptime > 0 and st.launches == 1
+        s = shares[0]
+        assert (s.job_id, s.channel_id, s.ntime, s.version, s.device_id) == (42, 2, f["time"], f["version"], "gpu-cuda0")
+        oh = oheader(oracle, f); oh.nonce = s.nonce
+        assert oracle.hash_header(oh) == s.hash
+
+
+def test_worker_job_switch_is_observed_via_job_id(miner):
+    """TestWorker_SetWorkJobChange (worker_test.go:142-175)."""
+    t = (1 << 236).to_bytes(32, "little")     # ~2^-20 of hashes: a steady trickle
+    with miner.Worker(miner.WorkerConfig(launch_log2=24)) as w:
+        w1, _ = easy_work(miner, job_id=1, target=t, repeat=True)
+        w.set_work(w1)
+        first = w.poll_shares(16, 5000)
+        assert first and all(s.job_id == 1 for s in first)
+        w2, _ = easy_work(miner, job_id=2, i=12, target=t, repeat=True)
+        seq = w.set_work(w2)
+        deadline = time.time() + 10
+        seen2 = False
+        while time.time() < deadline and not seen2:
+            seen2 = any(s.job_id == 2 and s.work_seq == seq for s in w.poll_shares(256, 200))
+        assert seen2
+        h0 = w.stats().hashes_total
+        time.sleep(0.2)
+        assert w.stats().hashes_total > h0   # monotone while working (HashrateMonitor, engine/stats.go:412-457)
+        w.set_work(None)                     # arbitration pause / curtailment (arbitrate.go:255-262)
+        assert not w.has_work()
+        time.sleep(0.3)
+        h1 = w.stats().hashes_total
+        time.sleep(0.2)
+        assert w.stats().hashes_total == h1
+
+
+def test_worker_set_work_aborts_a_long_launch_quickly(miner):
+    with miner.Worker(miner.WorkerConfig(launch_log2=32)) as w:
+        hard = (1).to_bytes(32, "little")
+        a, _ = easy_work(miner, job_id=1, target=hard, repeat=True)
+        w.set_work(a)
+        time.sleep(0.3)
+        b, f = easy_work(miner, job_id=2, i=13, nonce_count=1 << 16)
+        t0 = time.time()
+        w.set_work(b)
+        got = w.poll_shares(16, 5000)
+        dt = time.time() - t0
+        assert got and got[0].job_id == 2
+        assert dt < 0.25, f"job switch took {dt:.3f}s"   # a full 2^32 launch would take ~0.4 s
+
+
+def test_worker_queue_overflow_counts_drops(miner):
+    """Non-blocking send with a drop counter (worker.go:271-275)."""
+    with miner.Worker(miner.WorkerConfig(queue_capacity=100, launch_log2=16)) as w:
+        work, _ = easy_work(miner, nonce_count=1 << 12)
+        w.set_work(work)
+        assert w.wait_exhausted(10000)
+        st = w.stats()
+        assert st.shares_found == 1 << 12 and st.shares_dropped == (1 << 12) - 100
+        assert len(w.poll_shares(4096, 0)) == 100
+
+
+def test_worker_full_range_at_difficulty_one(miner):
+    """TestUpdateWork_PopulatesFullHeaderAndShareTarget (engine/run_test.go:356-396) in
+    spirit: the share echoes JobID / Version / NTime of the work it came from."""
+    f = W.genesis_fields()
+    with miner.Worker() as w:
+        w.set_work(miner.Work(job_id=5, channel_id=1, header=mheader(miner, f), nbits=f["bits"],
+                              target=miner.target_from_nbits(f["bits"])))
+        assert w.wait_exhausted(30000)
+        sh = w.poll_shares(16, 0)
+        assert [(s.nonce, s.hash.hex(), s.job_id, s.version, s.ntime) for s in sh] == \
+               [(W.GENESIS_NONCE, W.GENESIS_HASH_HEX, 5, 1, f["time"])]
+        st = w.stats()
+        assert st.hashes_total == 1 << 32 and st.hash_rate > 1e9
+
+
+def test_two_workers_partition_the_version_space(miner, oracle):
+    """static partition, no communication — version index k -> k mod G.
+    Runs both halves on device 0 when only one GPU is visible."""
+    from otedama_b200 import capi
+    ndev = capi.lib().otd_device_count()
+    c4 = W.config4_v2()
+    t = oracle.target_from_difficulty(2.0 ** -18)
+    base = dict(header=mheader(miner, c4), target=t, version_mask=c4["mask"], nonce_count=1 << 14)
+    whole = miner.scan(miner.Work(version_begin=0, version_count=32, **base))
+    parts = []
+    for g in range(2):
+        parts += miner.scan(miner.Work(version_begin=g, version_count=16, version_stride=2, **base),
+                            device=g % ndev).shares
+    assert sorted((s.version, s.nonce, s.hash) for s in parts) == sorted((s.version, s.nonce, s.hash) for s in whole.shares)
+    assert len(whole.shares) > 20
+
+
+def test_int_peak_microbenchmark_runs(miner):
+    names = miner.int_peak_modes()
+    assert "mix_alu" in names
+    ops, mhz, ms = miner.int_peak(names.index("lop3"), iters=256)
+    assert ops > 1e12 and 500 < mhz < 3000 and ms > 0

@@ -1,0 +1,189 @@
+"""The CPU oracle against the reference's own known-answer vectors
+(tests/golden/reference_vectors.json, transcribed from the reference tests) and
+against an independent implementation (hashlib/OpenSSL).  CPU only."""
+import hashlib
+import math
+import os
+import random
+import struct
+
+import pytest
+
+
+def test_sha256d_reference_kats(oracle, golden):
+    for backend in (0, 1):
+        used = oracle.set_backend(backend)
+        for v in golden["reference_vectors"]["sha256d"]:
+            got = oracle.sha256d(bytes.fromhex(v["input_hex"]))
+            assert got.hex() == v["hash_hex"], (v["cite"], used)
+    oracle.set_backend(-1)
+
+
+def test_genesis_nonce_and_header_layout(oracle, golden):
+    rv = golden["reference_vectors"]
+    raw = bytes.fromhex(rv["sha256d"][0]["input_hex"])
+    h = oracle.Header.parse(raw)
+    assert h.nonce == rv["genesis_nonce"]["nonce"] == 2083236893
+    assert h.bytes() == raw
+    assert oracle.hash_header(h).hex() == rv["sha256d"][0]["hash_hex"]
+    # TestHeader_Bytes_Roundtrip / TestHeader_NonceIsAtOffset76
+    hr = rv["header_roundtrip"]
+    x = oracle.Header(hr["version"], bytes(range(32)), bytes(255 - i for i in range(32)), hr["time"],
+                      hr["bits"], hr["nonce"])
+    b = x.bytes()
+    assert oracle.Header.parse(b) == x
+    assert struct.unpack_from("<I", b, hr["nonce_offset"])[0] == hr["nonce"]
+    assert struct.unpack_from("<I", oracle.Header(nonce=0x01020304).bytes(), 76)[0] == 0x01020304
+
+
+def test_scalar_and_shani_agree_with_hashlib(oracle):
+    rnd = random.Random(7)
+    for backend in (0, 1):
+        oracle.set_backend(backend)
+        for n in list(range(0, 130)) + [200, 255, 256, 1000, 4096]:
+            d = rnd.randbytes(n)
+            assert oracle.sha256d(d) == oracle.sha256d_hashlib(d)
+            assert oracle.sha256(d) == hashlib.sha256(d).digest()
+    oracle.set_backend(-1)
+
+
+def test_target_from_nbits_vectors(oracle, golden):
+    rv = golden["reference_vectors"]
+    for v in rv["target_from_nbits"]:
+        t = oracle.target_from_nbits(int(v["nbits"], 16))
+        assert t == bytes.fromhex(v["target_be_hex"])[::-1], v["cite"]
+    for v in rv["target_from_nbits_errors"]:
+        with pytest.raises(oracle.OracleError):
+            oracle.target_from_nbits(int(v["nbits"], 16))
+    for v in rv["target_from_nbits_ok_nonzero"]:
+        assert any(oracle.target_from_nbits(int(v["nbits"], 16)))
+
+
+def test_target_from_difficulty_vectors(oracle, golden):
+    d = golden["reference_vectors"]["difficulty"]
+    one = oracle.target_from_difficulty(d["one_equals_nbits"]["difficulty"])
+    assert one == oracle.target_from_nbits(int(d["one_equals_nbits"]["nbits"], 16))
+    easy = oracle.target_from_difficulty(d["easier"]["difficulty"])
+    hard = oracle.target_from_difficulty(d["harder"]["difficulty"])
+    assert oracle.less_or_equal(one, easy) and one != easy
+    assert oracle.less_or_equal(hard, one) and hard != one
+    for s in d["errors"]["values"]:
+        with pytest.raises(oracle.OracleError):
+            oracle.target_from_difficulty(float(s))
+    # power-of-two difficulties divide exactly
+    for k in range(-30, 200):
+        want = (0xFFFF << 208) >> k if k >= 0 else (0xFFFF << 208) << -k
+        if want == 0 or want.bit_length() > 256:
+            with pytest.raises(oracle.OracleError):
+                oracle.target_from_difficulty(2.0 ** k)
+        else:
+            assert int.from_bytes(oracle.target_from_difficulty(2.0 ** k), "little") == want
+    # floor of the exact rational whenever the 256-bit rounding cannot reach an integer
+    from fractions import Fraction
+    rnd = random.Random(3)
+    for _ in range(300):
+        x = rnd.uniform(0.5, 1e9)
+        exact = Fraction(0xFFFF << 208) / Fraction(x)
+        assert int.from_bytes(oracle.target_from_difficulty(x), "little") in (math.floor(exact), math.floor(exact) + 1)
+
+
+def test_nbits_from_target_vectors(oracle, golden):
+    for v in golden["reference_vectors"]["nbits_from_target"]:
+        t = oracle.target_from_nbits(int(v["from_nbits"], 16)) if "from_nbits" in v else bytes.fromhex(v["target_le_hex"])
+        got = oracle.nbits_from_target(t)
+        if "nbits" in v:
+            assert got == int(v["nbits"], 16), v["cite"]
+        if "exp" in v:
+            assert got >> 24 == v["exp"], v["cite"]
+        if "exp_min" in v:
+            assert got >> 24 >= v["exp_min"], v["cite"]
+
+
+def test_less_or_equal_and_meets_target(oracle, golden):
+    lv = golden["reference_vectors"]["less_or_equal"]
+    for a, b, want in lv["expect"]:
+        assert oracle.less_or_equal(bytes.fromhex(lv[a]), bytes.fromhex(lv[b])) is want
+    for v in golden["reference_vectors"]["meets_target"]:
+        assert oracle.meets_target(bytes([v["hash_fill"]]) * 32, int(v["nbits"], 16)) is v["meets"]
+    rnd = random.Random(11)
+    for _ in range(2000):
+        a, b = rnd.randbytes(32), rnd.randbytes(32)
+        if rnd.random() < 0.3:
+            k = rnd.randrange(33)          # share the k most significant bytes
+            b = b[:32 - k] + a[32 - k:]
+        assert oracle.less_or_equal(a, b) == (int.from_bytes(a, "little") <= int.from_bytes(b, "little"))
+
+
+def test_grind_matches_python_loop_and_finds_genesis(oracle):
+    from tests import workloads as wl
+    h = wl.genesis_header()
+    t1 = oracle.target_from_nbits(0x1D00FFFF)
+    shares, dropped, hashes = oracle.grind(h, t1, 2083236893 - 50000, 100000, threads=3)
+    assert [s.nonce for s in shares] == [2083236893] and dropped == 0 and hashes == 100000
+    assert shares[0].hash.hex() == "6fe28c0ab6f1b372c1a6a246ae63f74f931e8365e15a089c68d6190000000000"
+    assert shares[0].ntime == h.time and shares[0].version == h.version
+    easy = oracle.target_from_difficulty(2.0 ** -24)
+    for threads, mid in ((1, False), (4, False), (5, True)):
+        got, _, n = oracle.grind(wl.config2_header(7), easy, 1000, 20000, threads=threads, midstate=mid)
+        want = oracle.grind_py(wl.config2_header(7), easy, 1000, 20000)
+        assert n == 20000 and [(s.nonce, s.hash) for s in got] == [(s.nonce, s.hash) for s in want]
+        assert len(got) > 20
+    # window that wraps the top of the nonce space is covered once
+    got, _, n = oracle.grind(h, easy, (1 << 32) - 5000, 5000, threads=2)
+    assert n == 5000 and all(s.nonce >= (1 << 32) - 5000 for s in got)
+    # share cap -> dropped counter (worker.go:271-275)
+    got, dropped, _ = oracle.grind(h, b"\xff" * 32, 0, 1000, threads=2, cap=10)
+    assert len(got) == 10 and dropped == 990
+
+
+def test_golden_windows_reproduce(oracle, golden):
+    from tests import workloads as wl
+    doc = golden["synthetic_windows"]
+    case = doc["cases"][1]
+    h = wl.config2_header(case["index"])
+    assert h.bytes()[:76].hex() == case["header76_hex"]
+    shares, _, _ = oracle.grind(h, bytes.fromhex(case["target_hex"]), 0, 1 << 20, threads=os.cpu_count() or 1)
+    assert [s.nonce for s in shares] == [n for n in case["nonces"] if n < (1 << 20)]
+
+
+def test_full_genesis_scan_fixture(golden):
+    g = golden.get("genesis_full_scan")
+    if g is None:
+        pytest.skip("genesis_full_scan.json not generated yet")
+    assert g["hashes"] == 1 << 32
+    assert [s["nonce"] for s in g["shares"]] == [2083236893]
+    assert g["shares"][0]["hash"] == "6fe28c0ab6f1b372c1a6a246ae63f74f931e8365e15a089c68d6190000000000"
+
+
+def test_v1_merkle_root_unpinned_but_anchored(oracle, golden):
+    """No reference code exists for this; anchor: SHA256d(genesis coinbase tx) is
+    the merkle root inside the reference's genesis header vector."""
+    g = golden["reference_vectors"]["genesis_coinbase_tx"]
+    tx = bytes.fromhex(g["tx_hex"])
+    # split the tx as a pool would: coinb1 | extranonce1(4) | extranonce2(4) | coinb2
+    root = oracle.v1_merkle_root(tx[:50], tx[50:54], tx[54:58], tx[58:], [])
+    assert root.hex() == g["merkle_root_hex"]
+    assert golden["reference_vectors"]["sha256d"][0]["input_hex"][72:136] == g["merkle_root_hex"]
+    from tests import workloads as wl
+    v1 = wl.config3_v1()
+    for e, want in enumerate(golden["synthetic_windows"]["config3_roots_e0_7"]):
+        en2 = oracle.extranonce2_bytes(e, 8)
+        assert en2 == struct.pack("<Q", e)
+        r = oracle.v1_merkle_root(v1["coinb1"], v1["extranonce1"], en2, v1["coinb2"], v1["branches"])
+        assert r == oracle.v1_merkle_root_py(v1["coinb1"], v1["extranonce1"], en2, v1["coinb2"], v1["branches"])
+        assert r.hex() == want
+
+
+def test_bip320_versions(oracle, golden):
+    from tests import workloads as wl
+    v2 = wl.config4_v2()
+    seen = set()
+    for k in list(range(300)) + [4095, 65535]:
+        v = oracle.bip320_version(v2["version"], v2["mask"], k)
+        assert v == oracle.bip320_version_py(v2["version"], v2["mask"], k)
+        assert v & ~v2["mask"] == v2["version"] & ~v2["mask"]
+        assert (v & v2["mask"]) >> 13 == k
+        seen.add(v)
+    assert len(seen) == 302
+    for k, want in golden["synthetic_windows"]["config4_versions_k"].items():
+        assert oracle.bip320_version(v2["version"], v2["mask"], int(k)) == want
