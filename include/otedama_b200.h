@@ -187,17 +187,30 @@ int otd_worker_destroy(otd_worker_t* w);
 /* ------------------------------------------------------- synchronous scan --
  * One pass of grind (worker.go:216-282) over `work`'s whole search space on one
  * device, returning when done: the call tests and benchmarks use.  Writes up to
- * max_shares shares (sorted by extranonce2, version, nonce); *n_found gets the
- * total found (may exceed max_shares).  Optional outputs may be NULL:
+ * max_shares shares (sorted by extranonce2, version, nonce) and returns how many
+ * it wrote; *n_found gets the total found on the device, which can be larger when
+ * max_shares or the per-launch device ring (65536 entries) was too small.  Optional outputs may be NULL:
  * *hashes = candidates hashed, *device_ms = scan-kernel time by CUDA events on
  * the launching stream, *launches = scan kernel launches. */
 int otd_scan(int device_index, const otd_work_t* work, int kernel_variant, otd_share_t* out,
              uint32_t max_shares, uint64_t* n_found, uint64_t* hashes, double* device_ms,
              uint64_t* launches);
 
+/* Burst form for many independent headers (BASELINE configs[1]: genesis + 256
+ * synthetic headers): header i of the batch is searched over the nonce window
+ * against `target`; every launch is queued between one pair of CUDA events with
+ * no host synchronisation in between (*device_ms is that span).  Shares carry the
+ * header's batch index in job_id and come back sorted by (index, nonce).
+ * Returns the number of shares written. */
+int otd_scan_headers(int device_index, const otd_header_t* headers, uint32_t n_headers,
+                     const uint8_t target[32], uint32_t nonce_begin, uint64_t nonce_count,
+                     int kernel_variant, otd_share_t* out, uint32_t max_shares, uint64_t* n_found,
+                     uint64_t* hashes, double* device_ms, uint64_t* launches);
+
 /* Kernel variants compiled into the library: returns the count, fills
  * names[i] (each up to 32 bytes incl. NUL) when names != NULL. */
 int otd_scan_variants(char (*names)[32], int max_names);
+int otd_scan_default_variant(void);
 
 /* Job-preparation kernels exposed for parity tests (K3: extranonce2 roll +
  * coinbase hash + merkle fold; K2: rolled version). Fills n merkle roots

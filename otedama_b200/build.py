@@ -1,54 +1,101 @@
 """In-tree build of libotedama_b200.so (nvcc, sm_100a only).
 
-The library is the product: there is no CPU fallback, and importing
-``otedama_b200`` on a box where the .so is missing raises instead of degrading.
+The library is the product: there is no CPU fallback, and using ``otedama_b200``
+on a box where the .so is missing raises instead of degrading.  Every scan-kernel
+variant is its own translation unit (csrc/scan_variant.cu with -DOTD_VIDX=i), so
+the objects compile in parallel; objects are cached under csrc/_obj by content hash.
 """
 from __future__ import annotations
 
+import concurrent.futures as cf
+import hashlib
 import os
+import re
 import subprocess
 import sys
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_PKG)
 CSRC = os.path.join(_PKG, "csrc")
+OBJ = os.path.join(CSRC, "_obj")
 LIB_PATH = os.path.join(_PKG, "libotedama_b200.so")
-SOURCES = [os.path.join(CSRC, "otedama_b200.cu")]
-DEPS = SOURCES + [os.path.join(CSRC, f) for f in
-                  ("sha256_core.cuh", "scan_core.cuh", "scan_kernel.cuh", "job_kernels.cuh", "intpeak.cuh")] + \
+HEADERS = [os.path.join(CSRC, f) for f in ("sha256_core.cuh", "scan_core.cuh", "scan_kernel.cuh", "job_kernels.cuh",
+                                           "intpeak.cuh", "scan_variants.h")] + \
     [os.path.join(_ROOT, "include", "otedama_b200.h")]
+MAIN_SRC = os.path.join(CSRC, "otedama_b200.cu")
+VARIANT_SRC = os.path.join(CSRC, "scan_variant.cu")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",
-    "-Xcompiler", "-fPIC", "-shared",
+    "-Xcompiler", "-fPIC",
     "-Xptxas", "-v",
 ]
+
+
+def variant_indices() -> list:
+    txt = open(os.path.join(CSRC, "scan_variants.h")).read()
+    return [int(m) for m in re.findall(r"^\s*X\((\d+),", txt, flags=re.M)]
+
+
+def _digest(paths, extra="") -> str:
+    h = hashlib.sha256(extra.encode())
+    for p in paths:
+        h.update(open(p, "rb").read())
+    return h.hexdigest()[:16]
+
+
+def _compile(src, out, defines, log):
+    nvcc = os.environ.get("NVCC", "nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + defines + ["-c", "-o", out, src]
+    proc = subprocess.run(cmd, capture_output=True, text=True)
+    log.append(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
+    if proc.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + proc.stdout + proc.stderr)
+    return out
 
 
 def needs_build() -> bool:
     if not os.path.exists(LIB_PATH):
         return True
     t = os.path.getmtime(LIB_PATH)
-    return any(os.path.getmtime(d) > t for d in DEPS)
+    return any(os.path.getmtime(d) > t for d in HEADERS + [MAIN_SRC, VARIANT_SRC])
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, jobs: int = 0) -> str:
     if not force and not needs_build():
         return LIB_PATH
+    os.makedirs(OBJ, exist_ok=True)
+    log: list = []
+    tasks = []
+    key_main = _digest(HEADERS + [MAIN_SRC], " ".join(NVCC_FLAGS))
+    tasks.append((MAIN_SRC, os.path.join(OBJ, f"main_{key_main}.o"), []))
+    key_var = _digest(HEADERS[:3] + [HEADERS[5], VARIANT_SRC], " ".join(NVCC_FLAGS))
+    for i in variant_indices():
+        tasks.append((VARIANT_SRC, os.path.join(OBJ, f"variant{i}_{key_var}.o"), [f"-DOTD_VIDX={i}"]))
+    todo = [t for t in tasks if force or not os.path.exists(t[1])]
+    jobs = jobs or min(len(todo) or 1, os.cpu_count() or 1)
+    with cf.ThreadPoolExecutor(max_workers=jobs) as ex:
+        futs = [ex.submit(_compile, src, out, defs, log) for src, out, defs in todo]
+        for f in futs:
+            f.result()
+    keep = {t[1] for t in tasks}
+    for f in os.listdir(OBJ):  # drop stale objects
+        p = os.path.join(OBJ, f)
+        if p not in keep:
+            os.remove(p)
     nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-o", LIB_PATH] + SOURCES
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH] + [t[1] for t in tasks]
     proc = subprocess.run(cmd, capture_output=True, text=True)
-    log = os.path.join(_PKG, "build.log")
-    with open(log, "w") as f:
-        f.write(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
+    log.append(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
+    with open(os.path.join(_PKG, "build.log"), "w") as fh:
+        fh.write("\n".join(log))
     if proc.returncode != 0:
-        sys.stderr.write(proc.stdout + proc.stderr)
-        raise RuntimeError("nvcc failed building libotedama_b200.so (see %s)" % log)
+        raise RuntimeError("link failed:\n" + proc.stdout + proc.stderr)
     if verbose:
-        print(proc.stderr)
+        print("\n".join(log))
     return LIB_PATH
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose=True))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

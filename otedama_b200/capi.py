@@ -94,7 +94,11 @@ _SIGS = {
     "otd_worker_destroy": (c_int, [c_void_p]),
     "otd_scan": (c_int, [c_int, POINTER(CWork), c_int, POINTER(CShare), c_uint32, POINTER(c_uint64),
                          POINTER(c_uint64), POINTER(c_double), POINTER(c_uint64)]),
+    "otd_scan_headers": (c_int, [c_int, POINTER(CHeader), c_uint32, c_char_p, c_uint32, c_uint64, c_int,
+                                 POINTER(CShare), c_uint32, POINTER(c_uint64), POINTER(c_uint64),
+                                 POINTER(c_double), POINTER(c_uint64)]),
     "otd_scan_variants": (c_int, [c_void_p, c_int]),
+    "otd_scan_default_variant": (c_int, []),
     "otd_prepare_instances": (c_int, [c_int, POINTER(CWork), c_uint32, c_uint32, c_char_p,
                                       POINTER(c_uint32), POINTER(c_uint64), c_char_p]),
     "otd_int_peak": (c_int, [c_int, c_int, c_int, POINTER(c_double), POINTER(c_double), POINTER(c_double)]),

@@ -21,7 +21,8 @@ enum IntPeakMode {
     IPM_IMAD_WIDE = 7, // mul.wide.u32 chains                           (FMA pipe, 64-bit result)
     IPM_PRMT = 8,      // prmt chains                                   (ALU pipe)
     IPM_ALU_FMA = 9,   // 1 LOP3 : 1 IMAD interleaved                   (both pipes)
-    IPM_COUNT = 10
+    IPM_IMAD_HI = 10,  // mul.hi.u32 with a runtime multiplier          (FMA pipe)
+    IPM_COUNT = 11
 };
 
 #if defined(__CUDACC__)
@@ -38,7 +39,7 @@ __host__ __device__ constexpr int ip_ops_per_step(int mode)
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(256) int_peak_kernel(int iters, uint32_t one, uint32_t seed,
+__global__ void __launch_bounds__(1024) int_peak_kernel(int iters, uint32_t one, uint32_t seed,
                                                        uint32_t* sink, long long* cycles)
 {
     uint32_t x[kIpChains], y[kIpChains], z[kIpChains];
@@ -98,6 +99,8 @@ __global__ void __launch_bounds__(256) int_peak_kernel(int iters, uint32_t one, 
                         : "+r"(x[c]), "=r"(y[c]) : "r"(one));
                 } else if (MODE == IPM_PRMT) {
                     asm volatile("prmt.b32 %0, %0, %1, 0x0321;" : "+r"(x[c]) : "r"(y[c]));
+                } else if (MODE == IPM_IMAD_HI) {
+                    asm volatile("mul.hi.u32 %0, %0, %1;" : "+r"(x[c]) : "r"(seed));
                 } else if (MODE == IPM_ALU_FMA) {
                     asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
                     asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(z[c]));

@@ -28,6 +28,7 @@
 #include "intpeak.cuh"
 #include "job_kernels.cuh"
 #include "scan_kernel.cuh"
+#include "scan_variants.h"
 
 using namespace otd;
 
@@ -298,37 +299,17 @@ extern "C" int otd_meets_target(const uint8_t hash[32], uint32_t nbits)
 }
 
 // ------------------------------------------------------------ scan variants --
-typedef cudaError_t (*scan_launch_fn)(const JobConsts&, uint32_t, unsigned long long, uint32_t, RingHeader*,
-                                      RingEntry*, uint32_t, const unsigned int*, unsigned int, bool,
-                                      cudaStream_t);
-
-template <int V, int ITER>
-static cudaError_t launch_scan(const JobConsts& jc, uint32_t nonce_begin, unsigned long long count,
-                               uint32_t instance, RingHeader* hdr, RingEntry* ent, uint32_t cap,
-                               const unsigned int* stop, unsigned int gen, bool topzero, cudaStream_t st)
-{
-    constexpr unsigned long long tile = (unsigned long long)kScanBlock * V * ITER;
-    const unsigned grid = (unsigned)((count + tile - 1) / tile);
-    if (grid == 0) return cudaSuccess;
-    if (topzero)
-        scan_kernel<V, ITER, true><<<grid, kScanBlock, 0, st>>>(jc, nonce_begin, count, instance, hdr, ent, cap, stop, gen);
-    else
-        scan_kernel<V, ITER, false><<<grid, kScanBlock, 0, st>>>(jc, nonce_begin, count, instance, hdr, ent, cap, stop, gen);
-    return cudaGetLastError();
-}
-
 struct ScanVariant {
     const char* name;
     int v, iter;
-    scan_launch_fn fn;
+    unsigned knobs;
+    otd_scan_launch_fn fn;
 };
-static const ScanVariant kVariants[] = {
-    {"v1i16", 1, 16, launch_scan<1, 16>},
-    {"v2i8", 2, 8, launch_scan<2, 8>},
-    {"v4i4", 4, 4, launch_scan<4, 4>},
-};
+#define OTD_TABLE_ROW(idx, name, v, iter, kn) {name, v, iter, kn, otd_scan_launch_##idx},
+static const ScanVariant kVariants[] = {OTD_SCAN_VARIANTS(OTD_TABLE_ROW)};
+#undef OTD_TABLE_ROW
 static const int kNumVariants = (int)(sizeof kVariants / sizeof kVariants[0]);
-static const int kDefaultVariant = 1;
+static const int kDefaultVariant = OTD_DEFAULT_VARIANT;
 
 extern "C" int otd_scan_variants(char (*names)[32], int max_names)
 {
@@ -336,6 +317,7 @@ extern "C" int otd_scan_variants(char (*names)[32], int max_names)
         for (int i = 0; i < kNumVariants && i < max_names; i++) snprintf(names[i], 32, "%s", kVariants[i].name);
     return kNumVariants;
 }
+extern "C" int otd_scan_default_variant(void) { return kDefaultVariant; }
 
 // -------------------------------------------------------------- work copy --
 struct WorkCopy {
@@ -644,7 +626,6 @@ class Engine {
         if (launch_log2 == 0) launch_log2 = 32;
         launch_log2 = std::min(32u, std::max(16u, launch_log2));
         const uint64_t chunk = 1ull << launch_log2;
-        const bool topzero = wc.target_le[7] == 0;
         CU_TRY(cudaSetDevice(dev));
         int rc = upload_blob(wc);
         if (rc) return rc;
@@ -674,7 +655,7 @@ class Engine {
                     if (first_launch) { CU_TRY(cudaEventRecord(ev_first, stream)); first_launch = false; }
                     CU_TRY(cudaEventRecord(s.e0, stream));
                     cudaError_t le = kv.fn(h_consts[i], wc.w.nonce_begin + (uint32_t)off, cnt, (uint32_t)(inst & 0xffffffffu),
-                                           s.d_hdr, s.d_ent, cap, d_stop, gen, topzero, stream);
+                                           s.d_hdr, s.d_ent, cap, d_stop, gen, stream);
                     if (le != cudaSuccess) return fail(OTD_ECUDA, std::string("scan launch: ") + cudaGetErrorString(le));
                     CU_TRY(cudaEventRecord(s.e1, stream));
                     CU_TRY(cudaEventRecord(ev_last, stream));
@@ -761,7 +742,85 @@ extern "C" int otd_scan(int device_index, const otd_work_t* work, int kernel_var
     if (hashes) *hashes = rs.hashes;
     if (device_ms) *device_ms = rs.span_ms;
     if (launches) *launches = rs.launches;
-    return OTD_OK;
+    return (int)n;
+}
+
+// Burst scan of n independent headers (BASELINE configs[1] shape): all job
+// constants are folded up front, then every launch is queued back to back on
+// the stream between ONE pair of CUDA events — no host synchronisation inside
+// the timed region, inputs resident (kernel parameters) before it starts.
+extern "C" int otd_scan_headers(int device_index, const otd_header_t* headers, uint32_t n_headers,
+                                const uint8_t target[32], uint32_t nonce_begin, uint64_t nonce_count,
+                                int kernel_variant, otd_share_t* out, uint32_t max_shares, uint64_t* n_found,
+                                uint64_t* hashes, double* device_ms, uint64_t* launches)
+{
+    if (!headers || !target || n_headers == 0) return fail(OTD_EINVAL, "otd_scan_headers: bad argument");
+    if (max_shares && !out) return fail(OTD_EINVAL, "otd_scan_headers: out is NULL");
+    if (nonce_count == 0) nonce_count = 1ull << 32;
+    if ((uint64_t)nonce_begin + nonce_count > (1ull << 32)) return fail(OTD_EINVAL, "nonce window exceeds 2^32");
+    Engine* eng;
+    std::mutex* lock;
+    int rc = pool_engine(device_index, &eng, &lock);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> g(*lock);
+    if (kernel_variant < 0 || kernel_variant >= kNumVariants) kernel_variant = kDefaultVariant;
+    const ScanVariant& kv = kVariants[kernel_variant];
+    uint32_t tgt[8];
+    for (int i = 0; i < 8; i++) tgt[i] = get_le32(target + 4 * i);
+    std::vector<JobConsts> jcs(n_headers);
+    for (uint32_t i = 0; i < n_headers; i++) {
+        uint8_t hdr[80];
+        uint32_t mid[8], tail[3];
+        otd_header_bytes(&headers[i], hdr);
+        header_midstate(hdr, mid, tail);
+        fold_job_consts(mid, tail[0], tail[1], tail[2], tgt, &jcs[i]);
+    }
+    CU_TRY(cudaSetDevice(device_index));
+    Slot& s = eng->slot[0];
+    eng->gen += 1;
+    if (eng->gen == 0) eng->gen = 1;
+    eng->h_gen[0] = eng->gen;
+    CU_TRY(cudaMemcpyAsync(eng->d_stop, &eng->h_gen[0], sizeof(unsigned int), cudaMemcpyHostToDevice, eng->stream));
+    CU_TRY(cudaMemsetAsync(s.d_hdr, 0, sizeof(RingHeader), eng->stream));
+    CU_TRY(cudaStreamSynchronize(eng->stream));
+    CU_TRY(cudaEventRecord(eng->ev_first, eng->stream));
+    for (uint32_t i = 0; i < n_headers; i++) {
+        cudaError_t le = kv.fn(jcs[i], nonce_begin, nonce_count, i, s.d_hdr, s.d_ent, eng->cap, eng->d_stop, eng->gen,
+                               eng->stream);
+        if (le != cudaSuccess) return fail(OTD_ECUDA, std::string("scan launch: ") + cudaGetErrorString(le));
+    }
+    CU_TRY(cudaEventRecord(eng->ev_last, eng->stream));
+    CU_TRY(cudaMemcpyAsync(s.h_hdr, s.d_hdr, sizeof(RingHeader), cudaMemcpyDeviceToHost, eng->stream));
+    CU_TRY(cudaStreamSynchronize(eng->stream));
+    float ms = 0;
+    CU_TRY(cudaEventElapsedTime(&ms, eng->ev_first, eng->ev_last));
+    const uint32_t pushed = s.h_hdr->count;
+    const uint32_t n = std::min(pushed, eng->cap);
+    if (n) CU_TRY(cudaMemcpy(s.h_ent, s.d_ent, sizeof(RingEntry) * (size_t)n, cudaMemcpyDeviceToHost));
+    std::vector<otd_share_t> shares(n);
+    for (uint32_t i = 0; i < n; i++) {
+        otd_share_t& sh = shares[i];
+        memset(&sh, 0, sizeof sh);
+        const uint32_t hi = s.h_ent[i].instance;
+        sh.job_id = hi;  // the header's index in the batch
+        sh.nonce = s.h_ent[i].nonce;
+        sh.ntime = headers[hi].time;
+        sh.version = headers[hi].version;
+        memcpy(sh.hash, s.h_ent[i].hash, 32);
+        sh.work_seq = 1;
+        sh.device_index = device_index;
+    }
+    std::sort(shares.begin(), shares.end(), [](const otd_share_t& a, const otd_share_t& b) {
+        if (a.job_id != b.job_id) return a.job_id < b.job_id;
+        return a.nonce < b.nonce;
+    });
+    const size_t nw = std::min<size_t>(shares.size(), max_shares);
+    for (size_t i = 0; i < nw; i++) out[i] = shares[i];
+    if (n_found) *n_found = pushed;
+    if (hashes) *hashes = nonce_count * n_headers;
+    if (device_ms) *device_ms = ms;
+    if (launches) *launches = n_headers;
+    return (int)nw;
 }
 
 extern "C" int otd_prepare_instances(int device_index, const otd_work_t* work, uint32_t first, uint32_t n,
@@ -1008,7 +1067,7 @@ extern "C" int otd_worker_destroy(otd_worker_t* w)
 
 // ---------------------------------------------------------------- int peak --
 static const char* kIntPeakNames[IPM_COUNT] = {"lop3", "shf", "iadd3", "imad", "mix_alu",
-                                               "mix_dual", "mix_dual1", "imad_wide", "prmt", "alu_fma"};
+                                               "mix_dual", "mix_dual1", "imad_wide", "prmt", "alu_fma", "imad_hi"};
 
 extern "C" int otd_int_peak_modes(char (*names)[32], int max_names)
 {
@@ -1020,7 +1079,7 @@ extern "C" int otd_int_peak_modes(char (*names)[32], int max_names)
 template <int MODE>
 static cudaError_t launch_peak(int grid, int iters, uint32_t* sink, long long* cyc, cudaStream_t st)
 {
-    int_peak_kernel<MODE><<<grid, 256, 0, st>>>(iters, 1u, 12345u, sink, cyc);
+    int_peak_kernel<MODE><<<grid, 1024, 0, st>>>(iters, 1u, 12345u, sink, cyc);
     return cudaGetLastError();
 }
 
@@ -1033,8 +1092,9 @@ extern "C" int otd_int_peak(int device_index, int mode, int iters, double* ops_p
     CU_TRY(cudaSetDevice(device_index));
     int sms = 0;
     CU_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device_index));
-    const int blocks_per_sm = 4;  // 1024 threads/SM = 8 warps per scheduler
-    const int grid = sms * blocks_per_sm;
+    // one 1024-thread block per SM (8 warps per scheduler): block 0 then lives as long
+    // as the kernel, so its clock64 span over the event time is the SM clock
+    const int grid = sms;
     uint32_t* d_sink = nullptr;
     long long* d_cyc = nullptr;
     CU_TRY(cudaMalloc(&d_sink, sizeof(uint32_t)));
@@ -1046,7 +1106,7 @@ extern "C" int otd_int_peak(int device_index, int mode, int iters, double* ops_p
     CU_TRY(cudaEventCreate(&e1));
     typedef cudaError_t (*fn_t)(int, int, uint32_t*, long long*, cudaStream_t);
     static const fn_t fns[IPM_COUNT] = {launch_peak<0>, launch_peak<1>, launch_peak<2>, launch_peak<3>, launch_peak<4>,
-                                        launch_peak<5>, launch_peak<6>, launch_peak<7>, launch_peak<8>, launch_peak<9>};
+                                        launch_peak<5>, launch_peak<6>, launch_peak<7>, launch_peak<8>, launch_peak<9>, launch_peak<10>};
     cudaError_t e = cudaSuccess;
     for (int w = 0; w < 2 && e == cudaSuccess; w++) e = fns[mode](grid, iters / 4 + 1, d_sink, d_cyc, st);  // warm-up
     float ms = 0;
@@ -1059,7 +1119,7 @@ extern "C" int otd_int_peak(int device_index, int mode, int iters, double* ops_p
     if (e == cudaSuccess) e = cudaMemcpy(&cyc, d_cyc, sizeof cyc, cudaMemcpyDeviceToHost);
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st); cudaFree(d_sink); cudaFree(d_cyc);
     if (e != cudaSuccess) return fail(OTD_ECUDA, std::string("otd_int_peak: ") + cudaGetErrorString(e));
-    const double ops = (double)grid * 256.0 * (double)iters * kIpUnroll * kIpChains * ip_ops_per_step(mode);
+    const double ops = (double)grid * 1024.0 * (double)iters * kIpUnroll * kIpChains * ip_ops_per_step(mode);
     if (ops_per_s) *ops_per_s = ops / (ms * 1e-3);
     if (sm_mhz) *sm_mhz = (double)cyc / (ms * 1e-3) / 1e6;
     if (ms_out) *ms_out = ms;

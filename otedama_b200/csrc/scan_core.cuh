@@ -80,39 +80,229 @@ template <int V> OTD_HD vw<V> maj(const vw<V>& a, const vw<V>& b, const vw<V>& c
     return r;
 }
 
+// ---------------------------------------------------------------------------
+// Instruction placement.  sm_100 issues integer work on two pipes (measured on
+// B200): the ALU pipe (SHF/LOP3/IADD3/PRMT, 64 lanes/clk/SM) and
+// the FMA pipe (IMAD 64, IMAD.WIDE 60 lanes/clk/SM), ~119 lanes/clk/SM together.
+// A straight compile puts ~92% of SHA-256 on the ALU pipe and is bound by it;
+// the knobs below move selected adds to IMAD (x*1+y with a run-time 1) and
+// selected shifts/rotations to IMAD.WIDE (x * 2^(32-n): hi = x>>n, lo = x<<(32-n))
+// so that both pipes fill.  The run-time multipliers live in the constant bank.
+// ---------------------------------------------------------------------------
+enum : unsigned {
+    KN_E = 1u,       // e' = d + t1                 as IMAD
+    KN_HKW = 2u,     // h + K + W                   as 2 IMAD instead of IADD3
+    KN_T1 = 4u,      // (h+K+W) + Sigma1 + Ch       as 2 IMAD instead of IADD3
+    KN_A = 8u,       // t1 + Sigma0 + Maj           as 2 IMAD instead of IADD3
+    KN_W1 = 16u,     // schedule: last add          as IMAD
+    KN_W2 = 32u,     // schedule: first 3-input add as 2 IMAD
+    KN_SSHR = 64u,   // sigma0/1: the plain shift   via IMAD.WIDE (hi half)
+    KN_SROT = 128u,  // sigma0/1: both rotations    via IMAD.WIDE
+    KN_BS1 = 256u,   // Sigma1: two of three rotations via IMAD.WIDE
+    KN_BS0 = 512u,   // Sigma0: two of three rotations via IMAD.WIDE
+};
+
+struct PipeMults {  // run-time constants the compiler cannot fold (kernel parameter)
+    uint32_t one;                                  // 1
+    uint32_t m2, m13, m22, m6, m11, m25;           // 2^(32-n) for the Sigma rotations
+    uint32_t m7, m18, m3, m17, m19, m10;           // ... and for sigma0 / sigma1
+};
+OTD_HD PipeMults make_pipe_mults()
+{
+    PipeMults m;
+    m.one = 1u;
+    m.m2 = 1u << 30; m.m13 = 1u << 19; m.m22 = 1u << 10; m.m6 = 1u << 26; m.m11 = 1u << 21; m.m25 = 1u << 7;
+    m.m7 = 1u << 25; m.m18 = 1u << 14; m.m3 = 1u << 29; m.m17 = 1u << 15; m.m19 = 1u << 13; m.m10 = 1u << 22;
+    return m;
+}
+
+// a*1 + b on the FMA pipe
+OTD_HD uint32_t fma_add(uint32_t a, uint32_t b, uint32_t one)
+{
+#if defined(__CUDA_ARCH__)
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(b));
+    return d;
+#else
+    return a * one + b;
+#endif
+}
+// x * 2^(32-n) as a 64-bit product on the FMA pipe: hi = x >> n, lo = x << (32-n)
+OTD_HD void fma_wide(uint32_t x, uint32_t m, uint32_t& hi, uint32_t& lo)
+{
+#if defined(__CUDA_ARCH__)
+    asm("{ .reg .u64 t;\n mul.wide.u32 t, %2, %3;\n mov.b64 {%0, %1}, t; }" : "=r"(lo), "=r"(hi) : "r"(x), "r"(m));
+#else
+    const unsigned long long t = (unsigned long long)x * m;
+    hi = (uint32_t)(t >> 32);
+    lo = (uint32_t)t;
+#endif
+}
+
+template <unsigned KN>
+struct Ops {
+    PipeMults m;
+    OTD_HD uint32_t add_if(bool on_fma, uint32_t a, uint32_t b) const { return on_fma ? fma_add(a, b, m.one) : a + b; }
+    OTD_HD uint32_t add3_if(bool on_fma, uint32_t a, uint32_t b, uint32_t c) const
+    {
+        return on_fma ? fma_add(fma_add(a, b, m.one), c, m.one) : a + b + c;
+    }
+    OTD_HD uint32_t S1(uint32_t x) const
+    {
+        if (KN & KN_BS1) {
+            uint32_t h1, l1, h2, l2;
+            fma_wide(x, m.m11, h1, l1);
+            fma_wide(x, m.m25, h2, l2);
+            return rotr(x, 6) ^ h1 ^ l1 ^ h2 ^ l2;
+        }
+        return bsig1(x);
+    }
+    OTD_HD uint32_t S0(uint32_t x) const
+    {
+        if (KN & KN_BS0) {
+            uint32_t h1, l1, h2, l2;
+            fma_wide(x, m.m13, h1, l1);
+            fma_wide(x, m.m22, h2, l2);
+            return rotr(x, 2) ^ h1 ^ l1 ^ h2 ^ l2;
+        }
+        return bsig0(x);
+    }
+    OTD_HD uint32_t s0(uint32_t x) const
+    {
+        if (KN & KN_SROT) {
+            uint32_t h1, l1, h2, l2, h3, l3;
+            fma_wide(x, m.m7, h1, l1);
+            fma_wide(x, m.m18, h2, l2);
+            fma_wide(x, m.m3, h3, l3);
+            return h1 ^ l1 ^ h2 ^ l2 ^ h3;
+        }
+        if (KN & KN_SSHR) {
+            uint32_t h3, l3;
+            fma_wide(x, m.m3, h3, l3);
+            return rotr(x, 7) ^ rotr(x, 18) ^ h3;
+        }
+        return ssig0(x);
+    }
+    OTD_HD uint32_t s1(uint32_t x) const
+    {
+        if (KN & KN_SROT) {
+            uint32_t h1, l1, h2, l2, h3, l3;
+            fma_wide(x, m.m17, h1, l1);
+            fma_wide(x, m.m19, h2, l2);
+            fma_wide(x, m.m10, h3, l3);
+            return h1 ^ l1 ^ h2 ^ l2 ^ h3;
+        }
+        if (KN & KN_SSHR) {
+            uint32_t h3, l3;
+            fma_wide(x, m.m10, h3, l3);
+            return rotr(x, 17) ^ rotr(x, 19) ^ h3;
+        }
+        return ssig1(x);
+    }
+    // one message-schedule word: s1(w2) + w7 + s0(w15) + w16
+    OTD_HD uint32_t sched(uint32_t w2, uint32_t w7, uint32_t w15, uint32_t w16) const
+    {
+        const uint32_t t = add3_if(KN & KN_W2, s1(w2), w7, s0(w15));
+        return add_if(KN & KN_W1, t, w16);
+    }
+    // one round on scalars; kw = K + W already summed (or an immediate)
+    OTD_HD void round(uint32_t a, uint32_t b, uint32_t c, uint32_t& d, uint32_t e, uint32_t f, uint32_t g,
+                      uint32_t& h, uint32_t kw) const
+    {
+        const uint32_t hk = add_if(KN & KN_HKW, h, kw);
+        const uint32_t t1 = add3_if(KN & KN_T1, hk, S1(e), ch(e, f, g));
+        d = add_if(KN & KN_E, d, t1);
+        h = add3_if(KN & KN_A, t1, S0(a), maj(a, b, c));
+    }
+    // K + W (W per-candidate): IMAD when h+K+W is split onto the FMA pipe
+    OTD_HD uint32_t kplus(uint32_t w, uint32_t k) const { return add_if(KN & KN_HKW, w, k); }
+};
+
+// ---- vector wrappers over Ops -------------------------------------------------
+template <int V> OTD_HD uint32_t lane(const vw<V>& x, int i) { return x.x[i]; }
+template <int V> OTD_HD uint32_t lane(uint32_t x, int) { return x; }
+
 // One full round.  On return d holds the new e and h holds the new a; callers
 // rotate the argument order instead of moving registers.
-template <int V, typename KW>
-OTD_HD void rnd(const vw<V>& a, const vw<V>& b, const vw<V>& c, vw<V>& d, const vw<V>& e,
+template <int V, unsigned KN, typename KW>
+OTD_HD void rnd(const Ops<KN>& op, const vw<V>& a, const vw<V>& b, const vw<V>& c, vw<V>& d, const vw<V>& e,
                 const vw<V>& f, const vw<V>& g, vw<V>& h, const KW& kw)
 {
-    vw<V> t1 = h + bsig1(e) + ch(e, f, g) + kw;
-    d = d + t1;
-    h = t1 + bsig0(a) + maj(a, b, c);
+#pragma unroll
+    for (int i = 0; i < V; i++) op.round(a.x[i], b.x[i], c.x[i], d.x[i], e.x[i], f.x[i], g.x[i], h.x[i], lane<V>(kw, i));
 }
 // e-chain only (the a value produced here is never consumed).
-template <int V, typename KW>
-OTD_HD void rnd_e(vw<V>& d, const vw<V>& e, const vw<V>& f, const vw<V>& g, const vw<V>& h,
-                  const KW& kw)
+template <int V, unsigned KN>
+OTD_HD void rnd_e(const Ops<KN>& op, vw<V>& d, const vw<V>& e, const vw<V>& f, const vw<V>& g, const vw<V>& h,
+                  const vw<V>& kw)
 {
-    d = d + h + bsig1(e) + ch(e, f, g) + kw;
+#pragma unroll
+    for (int i = 0; i < V; i++) {
+        const uint32_t hk = op.add_if(KN & KN_HKW, h.x[i], kw.x[i]);
+        const uint32_t t1 = op.add3_if(KN & KN_T1, hk, op.S1(e.x[i]), ch(e.x[i], f.x[i], g.x[i]));
+        d.x[i] = op.add_if(KN & KN_E, d.x[i], t1);
+    }
+}
+template <int V, unsigned KN>
+OTD_HD vw<V> kpl(const Ops<KN>& op, const vw<V>& w, uint32_t k)
+{
+    vw<V> r;
+#pragma unroll
+    for (int i = 0; i < V; i++) r.x[i] = op.kplus(w.x[i], k);
+    return r;
+}
+template <int V, unsigned KN>
+OTD_HD vw<V> sched(const Ops<KN>& op, const vw<V>& w2, const vw<V>& w7, const vw<V>& w15, const vw<V>& w16)
+{
+    vw<V> r;
+#pragma unroll
+    for (int i = 0; i < V; i++) r.x[i] = op.sched(w2.x[i], w7.x[i], w15.x[i], w16.x[i]);
+    return r;
+}
+template <int V, unsigned KN> OTD_HD vw<V> vs0(const Ops<KN>& op, const vw<V>& x)
+{
+    vw<V> r;
+#pragma unroll
+    for (int i = 0; i < V; i++) r.x[i] = op.s0(x.x[i]);
+    return r;
+}
+template <int V, unsigned KN> OTD_HD vw<V> vs1(const Ops<KN>& op, const vw<V>& x)
+{
+    vw<V> r;
+#pragma unroll
+    for (int i = 0; i < V; i++) r.x[i] = op.s1(x.x[i]);
+    return r;
+}
+template <int V, unsigned KN> OTD_HD vw<V> vS0(const Ops<KN>& op, const vw<V>& x)
+{
+    vw<V> r;
+#pragma unroll
+    for (int i = 0; i < V; i++) r.x[i] = op.S0(x.x[i]);
+    return r;
+}
+template <int V, unsigned KN> OTD_HD vw<V> vS1(const Ops<KN>& op, const vw<V>& x)
+{
+    vw<V> r;
+#pragma unroll
+    for (int i = 0; i < V; i++) r.x[i] = op.S1(x.x[i]);
+    return r;
 }
 
 // 8 rounds starting at round index R with schedule words w[R..R+7] already final.
-#define OTD_R8(R, a, b, c, d, e, f, g, h)      \
-    rnd(a, b, c, d, e, f, g, h, w[(R) + 0] + Kc((R) + 0)); \
-    rnd(h, a, b, c, d, e, f, g, w[(R) + 1] + Kc((R) + 1)); \
-    rnd(g, h, a, b, c, d, e, f, w[(R) + 2] + Kc((R) + 2)); \
-    rnd(f, g, h, a, b, c, d, e, w[(R) + 3] + Kc((R) + 3)); \
-    rnd(e, f, g, h, a, b, c, d, w[(R) + 4] + Kc((R) + 4)); \
-    rnd(d, e, f, g, h, a, b, c, w[(R) + 5] + Kc((R) + 5)); \
-    rnd(c, d, e, f, g, h, a, b, w[(R) + 6] + Kc((R) + 6)); \
-    rnd(b, c, d, e, f, g, h, a, w[(R) + 7] + Kc((R) + 7));
+#define OTD_R8(R, a, b, c, d, e, f, g, h)                                \
+    rnd(op, a, b, c, d, e, f, g, h, kpl(op, w[(R) + 0], Kc((R) + 0)));   \
+    rnd(op, h, a, b, c, d, e, f, g, kpl(op, w[(R) + 1], Kc((R) + 1)));   \
+    rnd(op, g, h, a, b, c, d, e, f, kpl(op, w[(R) + 2], Kc((R) + 2)));   \
+    rnd(op, f, g, h, a, b, c, d, e, kpl(op, w[(R) + 3], Kc((R) + 3)));   \
+    rnd(op, e, f, g, h, a, b, c, d, kpl(op, w[(R) + 4], Kc((R) + 4)));   \
+    rnd(op, d, e, f, g, h, a, b, c, kpl(op, w[(R) + 5], Kc((R) + 5)));   \
+    rnd(op, c, d, e, f, g, h, a, b, kpl(op, w[(R) + 6], Kc((R) + 6)));   \
+    rnd(op, b, c, d, e, f, g, h, a, kpl(op, w[(R) + 7], Kc((R) + 7)));
 
 // Returns e after round 60 of the second hash for V candidates whose block-2
 // word 3 (the big-endian nonce word) is w3.  Digest word 7 = IV7 + result.
-template <int V>
-OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3)
+template <int V, unsigned KN>
+OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
 {
     vw<V> w[64];
     vw<V> a, b, c, d, e, f, g, h;
@@ -124,99 +314,129 @@ OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3)
 
     // rounds 4..6: h and d are still job constants (k4/k5/k6 carry h + K + W)
     {
-        vw<V> t1 = bsig1(e) + ch(e, f, g) + jc.k4;                  // round 4
+        vw<V> t1 = vS1(op, e) + ch(e, f, g) + jc.k4;                  // round 4
         vw<V> e5 = t1 + jc.c3;
-        vw<V> a5 = t1 + bsig0(a) + maj(a, b, c);
-        t1 = bsig1(e5) + ch(e5, e, f) + jc.k5;                      // round 5
+        vw<V> a5 = t1 + vS0(op, a) + maj(a, b, c);
+        t1 = vS1(op, e5) + ch(e5, e, f) + jc.k5;                      // round 5
         vw<V> e6 = t1 + jc.b3;
-        vw<V> a6 = t1 + bsig0(a5) + maj(a5, a, b);
-        t1 = bsig1(e6) + ch(e6, e5, e) + jc.k6;                     // round 6
+        vw<V> a6 = t1 + vS0(op, a5) + maj(a5, a, b);
+        t1 = vS1(op, e6) + ch(e6, e5, e) + jc.k6;                     // round 6
         vw<V> e7 = t1 + jc.a3;
-        vw<V> a7 = t1 + bsig0(a6) + maj(a6, a5, a);
+        vw<V> a7 = t1 + vS0(op, a6) + maj(a6, a5, a);
         // state entering round 7: (a7, a6, a5, a4, e7, e6, e5, e4)
         vw<V> a4 = a, e4 = e;
         a = a7; b = a6; c = a5; d = a4; e = e7; f = e6; g = e5; h = e4;
     }
     // rounds 7..15: W5..W14 = 0, W15 = 0x280
-    rnd(a, b, c, d, e, f, g, h, Kc(7));
-    rnd(h, a, b, c, d, e, f, g, Kc(8));
-    rnd(g, h, a, b, c, d, e, f, Kc(9));
-    rnd(f, g, h, a, b, c, d, e, Kc(10));
-    rnd(e, f, g, h, a, b, c, d, Kc(11));
-    rnd(d, e, f, g, h, a, b, c, Kc(12));
-    rnd(c, d, e, f, g, h, a, b, Kc(13));
-    rnd(b, c, d, e, f, g, h, a, Kc(14));
-    rnd(a, b, c, d, e, f, g, h, Kc(15) + 0x280u);
+    rnd(op, a, b, c, d, e, f, g, h, Kc(7));
+    rnd(op, h, a, b, c, d, e, f, g, Kc(8));
+    rnd(op, g, h, a, b, c, d, e, f, Kc(9));
+    rnd(op, f, g, h, a, b, c, d, e, Kc(10));
+    rnd(op, e, f, g, h, a, b, c, d, Kc(11));
+    rnd(op, d, e, f, g, h, a, b, c, Kc(12));
+    rnd(op, c, d, e, f, g, h, a, b, Kc(13));
+    rnd(op, b, c, d, e, f, g, h, a, Kc(14));
+    rnd(op, a, b, c, d, e, f, g, h, Kc(15) + 0x280u);
     // schedule words 18..33 (16, 17 are job constants)
-    w[18] = ssig0(w3) + jc.c18;
+    w[18] = vs0(op, w3) + jc.c18;
     w[19] = w3 + jc.c19;
-    w[20] = ssig1(w[18]) + 0x80000000u;
-    w[21] = ssig1(w[19]);
-    w[22] = ssig1(w[20]) + 0x280u;
-    w[23] = ssig1(w[21]) + jc.w16;
-    w[24] = ssig1(w[22]) + jc.w17;
-    w[25] = ssig1(w[23]) + w[18];
-    w[26] = ssig1(w[24]) + w[19];
-    w[27] = ssig1(w[25]) + w[20];
-    w[28] = ssig1(w[26]) + w[21];
-    w[29] = ssig1(w[27]) + w[22];
-    w[30] = ssig1(w[28]) + w[23] + ssig0(0x280u);
-    w[31] = ssig1(w[29]) + w[24] + jc.c31;
-    w[32] = ssig1(w[30]) + w[25] + jc.c32;
-    w[33] = ssig1(w[31]) + w[26] + ssig0(w[18]) + jc.w17;
+    w[20] = vs1(op, w[18]) + 0x80000000u;
+    w[21] = vs1(op, w[19]);
+    w[22] = vs1(op, w[20]) + 0x280u;
+    w[23] = vs1(op, w[21]) + jc.w16;
+    w[24] = vs1(op, w[22]) + jc.w17;
+    w[25] = vs1(op, w[23]) + w[18];
+    w[26] = vs1(op, w[24]) + w[19];
+    w[27] = vs1(op, w[25]) + w[20];
+    w[28] = vs1(op, w[26]) + w[21];
+    w[29] = vs1(op, w[27]) + w[22];
+    w[30] = vs1(op, w[28]) + w[23] + ssig0(0x280u);
+    w[31] = vs1(op, w[29]) + w[24] + jc.c31;
+    w[32] = vs1(op, w[30]) + w[25] + jc.c32;
+    w[33] = sched(op, w[31], w[26], w[18], bc<V>(jc.w17));
 #pragma unroll
-    for (int i = 34; i < 64; i++) w[i] = ssig1(w[i - 2]) + w[i - 7] + ssig0(w[i - 15]) + w[i - 16];
+    for (int i = 34; i < 64; i++) w[i] = sched(op, w[i - 2], w[i - 7], w[i - 15], w[i - 16]);
 
-    rnd(h, a, b, c, d, e, f, g, jc.kw16);
-    rnd(g, h, a, b, c, d, e, f, jc.kw17);
-    rnd(f, g, h, a, b, c, d, e, w[18] + Kc(18));
-    rnd(e, f, g, h, a, b, c, d, w[19] + Kc(19));
-    rnd(d, e, f, g, h, a, b, c, w[20] + Kc(20));
-    rnd(c, d, e, f, g, h, a, b, w[21] + Kc(21));
-    rnd(b, c, d, e, f, g, h, a, w[22] + Kc(22));
-    rnd(a, b, c, d, e, f, g, h, w[23] + Kc(23));
-    rnd(h, a, b, c, d, e, f, g, w[24] + Kc(24));
-    rnd(g, h, a, b, c, d, e, f, w[25] + Kc(25));
-    rnd(f, g, h, a, b, c, d, e, w[26] + Kc(26));
-    rnd(e, f, g, h, a, b, c, d, w[27] + Kc(27));
-    rnd(d, e, f, g, h, a, b, c, w[28] + Kc(28));
-    rnd(c, d, e, f, g, h, a, b, w[29] + Kc(29));
-    rnd(b, c, d, e, f, g, h, a, w[30] + Kc(30));
-    rnd(a, b, c, d, e, f, g, h, w[31] + Kc(31));
+    rnd(op, h, a, b, c, d, e, f, g, jc.kw16);
+    rnd(op, g, h, a, b, c, d, e, f, jc.kw17);
+    rnd(op, f, g, h, a, b, c, d, e, kpl(op, w[18], Kc(18)));
+    rnd(op, e, f, g, h, a, b, c, d, kpl(op, w[19], Kc(19)));
+    rnd(op, d, e, f, g, h, a, b, c, kpl(op, w[20], Kc(20)));
+    rnd(op, c, d, e, f, g, h, a, b, kpl(op, w[21], Kc(21)));
+    rnd(op, b, c, d, e, f, g, h, a, kpl(op, w[22], Kc(22)));
+    rnd(op, a, b, c, d, e, f, g, h, kpl(op, w[23], Kc(23)));
+    rnd(op, h, a, b, c, d, e, f, g, kpl(op, w[24], Kc(24)));
+    rnd(op, g, h, a, b, c, d, e, f, kpl(op, w[25], Kc(25)));
+    rnd(op, f, g, h, a, b, c, d, e, kpl(op, w[26], Kc(26)));
+    rnd(op, e, f, g, h, a, b, c, d, kpl(op, w[27], Kc(27)));
+    rnd(op, d, e, f, g, h, a, b, c, kpl(op, w[28], Kc(28)));
+    rnd(op, c, d, e, f, g, h, a, b, kpl(op, w[29], Kc(29)));
+    rnd(op, b, c, d, e, f, g, h, a, kpl(op, w[30], Kc(30)));
+    rnd(op, a, b, c, d, e, f, g, h, kpl(op, w[31], Kc(31)));
     // after round 31 the "a" role is back on register h
     OTD_R8(32, h, a, b, c, d, e, f, g)
     OTD_R8(40, h, a, b, c, d, e, f, g)
     OTD_R8(48, h, a, b, c, d, e, f, g)
     OTD_R8(56, h, a, b, c, d, e, f, g)
-    // 64 - 3 = 61 rotations since the state was named at round 3... the role
-    // order now is (h,a,b,c,d,e,f,g) = (A,B,C,D,E,F,G,H).
+    // the role order now is (h,a,b,c,d,e,f,g) = (A,B,C,D,E,F,G,H).
 
     // ---------------- hash 2 ----------------
     // message = digest of hash 1 (state + midstate), padding, length 256 bits
     w[0] = h + jc.mid[0]; w[1] = a + jc.mid[1]; w[2] = b + jc.mid[2]; w[3] = c + jc.mid[3];
     w[4] = d + jc.mid[4]; w[5] = e + jc.mid[5]; w[6] = f + jc.mid[6]; w[7] = g + jc.mid[7];
-    w[8] = bc<V>(0x80000000u);
+    // W8 = 0x80000000, W9..14 = 0, W15 = 0x100: written out so the zero terms vanish
+    w[16] = vs0(op, w[1]) + w[0];
+    w[17] = vs0(op, w[2]) + w[1] + ssig1(0x100u);
+    w[18] = vs1(op, w[16]) + vs0(op, w[3]) + w[2];
+    w[19] = vs1(op, w[17]) + vs0(op, w[4]) + w[3];
+    w[20] = vs1(op, w[18]) + vs0(op, w[5]) + w[4];
+    w[21] = vs1(op, w[19]) + vs0(op, w[6]) + w[5];
+    w[22] = sched(op, w[20], bc<V>(0x100u), w[7], w[6]);
+    w[23] = vs1(op, w[21]) + w[16] + w[7] + ssig0(0x80000000u);
+    w[24] = vs1(op, w[22]) + w[17] + 0x80000000u;
+    w[25] = vs1(op, w[23]) + w[18];
+    w[26] = vs1(op, w[24]) + w[19];
+    w[27] = vs1(op, w[25]) + w[20];
+    w[28] = vs1(op, w[26]) + w[21];
+    w[29] = vs1(op, w[27]) + w[22];
+    w[30] = vs1(op, w[28]) + w[23] + ssig0(0x100u);
+    w[31] = vs1(op, w[29]) + w[24] + vs0(op, w[16]) + 0x100u;
 #pragma unroll
-    for (int i = 9; i < 15; i++) w[i] = bc<V>(0u);
-    w[15] = bc<V>(0x100u);
-#pragma unroll
-    for (int i = 16; i < 61; i++) w[i] = ssig1(w[i - 2]) + w[i - 7] + ssig0(w[i - 15]) + w[i - 16];
+    for (int i = 32; i < 61; i++) w[i] = sched(op, w[i - 2], w[i - 7], w[i - 15], w[i - 16]);
 
     a = bc<V>(IV0); b = bc<V>(IV1); c = bc<V>(IV2); d = bc<V>(IV3);
     e = bc<V>(IV4); f = bc<V>(IV5); g = bc<V>(IV6); h = bc<V>(IV7);
-    OTD_R8(0, a, b, c, d, e, f, g, h)
-    OTD_R8(8, a, b, c, d, e, f, g, h)
+    // rounds 0..3 still see compile-time constants (IV words) in the state: plain C so they fold
+    {
+        const Ops<0> fold{};
+        rnd(fold, a, b, c, d, e, f, g, h, w[0] + Kc(0));
+        rnd(fold, h, a, b, c, d, e, f, g, w[1] + Kc(1));
+        rnd(fold, g, h, a, b, c, d, e, f, w[2] + Kc(2));
+        rnd(fold, f, g, h, a, b, c, d, e, w[3] + Kc(3));
+    }
+    rnd(op, e, f, g, h, a, b, c, d, kpl(op, w[4], Kc(4)));
+    rnd(op, d, e, f, g, h, a, b, c, kpl(op, w[5], Kc(5)));
+    rnd(op, c, d, e, f, g, h, a, b, kpl(op, w[6], Kc(6)));
+    rnd(op, b, c, d, e, f, g, h, a, kpl(op, w[7], Kc(7)));
+    rnd(op, a, b, c, d, e, f, g, h, Kc(8) + 0x80000000u);
+    rnd(op, h, a, b, c, d, e, f, g, Kc(9));
+    rnd(op, g, h, a, b, c, d, e, f, Kc(10));
+    rnd(op, f, g, h, a, b, c, d, e, Kc(11));
+    rnd(op, e, f, g, h, a, b, c, d, Kc(12));
+    rnd(op, d, e, f, g, h, a, b, c, Kc(13));
+    rnd(op, c, d, e, f, g, h, a, b, Kc(14));
+    rnd(op, b, c, d, e, f, g, h, a, Kc(15) + 0x100u);
     OTD_R8(16, a, b, c, d, e, f, g, h)
     OTD_R8(24, a, b, c, d, e, f, g, h)
     OTD_R8(32, a, b, c, d, e, f, g, h)
     OTD_R8(40, a, b, c, d, e, f, g, h)
     OTD_R8(48, a, b, c, d, e, f, g, h)
     // round 56 full, rounds 57..60 e-chain only
-    rnd(a, b, c, d, e, f, g, h, w[56] + Kc(56));
-    rnd_e(c, d, e, f, g, w[57] + Kc(57));
-    rnd_e(b, c, d, e, f, w[58] + Kc(58));
-    rnd_e(a, b, c, d, e, w[59] + Kc(59));
-    rnd_e(h, a, b, c, d, w[60] + Kc(60));
+    rnd(op, a, b, c, d, e, f, g, h, kpl(op, w[56], Kc(56)));
+    rnd_e(op, c, d, e, f, g, kpl(op, w[57], Kc(57)));
+    rnd_e(op, b, c, d, e, f, kpl(op, w[58], Kc(58)));
+    rnd_e(op, a, b, c, d, e, kpl(op, w[59], Kc(59)));
+    rnd_e(op, h, a, b, c, d, kpl(op, w[60], Kc(60)));
     return h;
 }
 

@@ -3,8 +3,9 @@
 // Replaces Worker.grind (internal/miner/worker.go:216-282): every thread takes
 // V*ITER candidates of the window [nonce_begin, nonce_begin+count), runs the
 // register-resident folded double compression (scan_core.cuh) and tests the
-// most significant word of the little-endian hash integer.  Survivors (about
-// 2^-32 of candidates at difficulty >= 1) are re-hashed in full, compared
+// most significant word of the little-endian hash integer against the target's
+// (early reject on the final state word).  Survivors (about 2^-32 of candidates
+// at difficulty >= 1) are re-hashed in full, compared
 // against the whole 256-bit target exactly like Hash.LessOrEqual
 // (internal/miner/sha256d.go:93-103) and compacted into the share ring with one
 // warp ballot and one atomicAdd per warp.
@@ -34,7 +35,7 @@ constexpr int kScanBlock = 256;
 #if defined(__CUDACC__)
 
 // Full check of one surviving candidate; fills digest words when it is a share.
-__device__ __noinline__ bool confirm_candidate(const JobConsts& jc, uint32_t nonce, uint32_t dig[8])
+static __device__ __noinline__ bool confirm_candidate(const JobConsts& jc, uint32_t nonce, uint32_t dig[8])
 {
     sha256d_from_consts(jc, nonce, dig);
     return digest_le_target(dig, jc.target);
@@ -65,16 +66,18 @@ __device__ __forceinline__ void ring_push_warp(bool hit, uint32_t nonce, uint32_
 }
 
 // V: candidates interleaved per thread; ITER: sequential batches per thread;
-// TOPZERO: target < 2^224 (difficulty >= 1), so the cheap test is H7 == 0.
-template <int V, int ITER, bool TOPZERO>
+// KN: instruction-placement knobs (scan_core.cuh).
+template <int V, int ITER, unsigned KN>
 __global__ void __launch_bounds__(kScanBlock)
-scan_kernel(const __grid_constant__ JobConsts jc, uint32_t nonce_begin, unsigned long long count,
+scan_kernel(const __grid_constant__ JobConsts jc, const __grid_constant__ PipeMults pm,
+            uint32_t nonce_begin, unsigned long long count,
             uint32_t instance, RingHeader* ring, RingEntry* entries, uint32_t cap,
             const unsigned int* stop_gen, unsigned int my_gen)
 {
     // A newer job (or set_work(NULL)) bumps *stop_gen: blocks not yet started exit at once.
     if (*reinterpret_cast<const volatile unsigned int*>(stop_gen) != my_gen) return;
 
+    const Ops<KN> op{pm};
     constexpr unsigned long long kTile = (unsigned long long)kScanBlock * V * ITER;
     const unsigned long long tile0 = (unsigned long long)blockIdx.x * kTile + threadIdx.x;
 
@@ -85,14 +88,13 @@ scan_kernel(const __grid_constant__ JobConsts jc, uint32_t nonce_begin, unsigned
 #pragma unroll
         for (int v = 0; v < V; v++)
             w3.x[v] = __byte_perm(nonce_begin + (uint32_t)idx0 + (uint32_t)(v * kScanBlock), 0, 0x0123);
-        const vw<V> e60 = scan_core<V>(jc, w3);
+        const vw<V> e60 = scan_core<V, KN>(jc, w3, op);
 
         unsigned cmask = 0;
 #pragma unroll
         for (int v = 0; v < V; v++) {
-            bool cnd;
-            if (TOPZERO) cnd = (e60.x[v] == kE60ForZeroTop);
-            else cnd = __byte_perm(e60.x[v] + IV7, 0, 0x0123) <= jc.target[7];
+            // most significant word of the little-endian hash integer vs the target's
+            const bool cnd = __byte_perm(e60.x[v] + IV7, 0, 0x0123) <= jc.target[7];
             cmask |= (cnd ? 1u : 0u) << v;
         }
         if (__any_sync(0xffffffffu, cmask != 0)) {  // rare, warp-uniform

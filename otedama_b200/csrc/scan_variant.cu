@@ -1,0 +1,50 @@
+// scan_variant.cu — one scan-kernel variant per translation unit: compile with
+// -DOTD_VIDX=<index into OTD_SCAN_VARIANTS>.
+#include "scan_kernel.cuh"
+#include "scan_variants.h"
+
+#ifndef OTD_VIDX
+#error "compile with -DOTD_VIDX=<variant index>"
+#endif
+
+namespace {
+template <int V, int ITER, unsigned KN>
+cudaError_t launch(const otd::JobConsts& jc, uint32_t nonce_begin, unsigned long long count, uint32_t instance,
+                   otd::RingHeader* hdr, otd::RingEntry* ent, uint32_t cap, const unsigned int* stop,
+                   unsigned int gen, cudaStream_t st)
+{
+    constexpr unsigned long long tile = (unsigned long long)otd::kScanBlock * V * ITER;
+    const unsigned grid = (unsigned)((count + tile - 1) / tile);
+    if (grid == 0) return cudaSuccess;
+    otd::scan_kernel<V, ITER, KN><<<grid, otd::kScanBlock, 0, st>>>(jc, otd::make_pipe_mults(), nonce_begin, count,
+                                                                      instance, hdr, ent, cap, stop, gen);
+    return cudaGetLastError();
+}
+}  // namespace
+
+// The selected variant's parameters, picked out of the list at compile time.
+namespace {
+struct Sel {
+    int v, iter;
+    unsigned kn;
+};
+constexpr Sel select(int want)
+{
+#define OTD_PICK(idx, name, v, iter, kn) \
+    if (want == idx) return Sel{v, iter, kn};
+    OTD_SCAN_VARIANTS(OTD_PICK)
+#undef OTD_PICK
+    return Sel{1, 16, 0u};
+}
+constexpr Sel kSel = select(OTD_VIDX);
+}  // namespace
+
+#define OTD_FN_NAME_(i) otd_scan_launch_##i
+#define OTD_FN_NAME(i) OTD_FN_NAME_(i)
+
+cudaError_t OTD_FN_NAME(OTD_VIDX)(const otd::JobConsts& jc, uint32_t nonce_begin, unsigned long long count,
+                                  uint32_t instance, otd::RingHeader* hdr, otd::RingEntry* ent, uint32_t cap,
+                                  const unsigned int* stop, unsigned int gen, cudaStream_t st)
+{
+    return launch<kSel.v, kSel.iter, kSel.kn>(jc, nonce_begin, count, instance, hdr, ent, cap, stop, gen, st);
+}

@@ -227,17 +227,37 @@ def scan(work: Work, device: int = 0, variant: int = -1, max_shares: int = 1 << 
     out = (CShare * max_shares)()
     found, hashes, launches = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
     ms = ctypes.c_double()
-    check(lib().otd_scan(device, ctypes.byref(cw), variant, out, max_shares, ctypes.byref(found),
-                         ctypes.byref(hashes), ctypes.byref(ms), ctypes.byref(launches)))
-    n = min(found.value, max_shares)
+    n = check(lib().otd_scan(device, ctypes.byref(cw), variant, out, max_shares, ctypes.byref(found),
+                             ctypes.byref(hashes), ctypes.byref(ms), ctypes.byref(launches)))
     did = _device_id(device)
     del keep
     return ScanResult([_share_from_c(out[i], did) for i in range(n)], found.value, hashes.value,
                       ms.value, launches.value)
 
 
+def scan_headers(headers: Sequence[Header], target: bytes, nonce_begin: int = 0, nonce_count: int = 0,
+                 device: int = 0, variant: int = -1, max_shares: int = 1 << 16) -> ScanResult:
+    """Burst scan of many independent headers (one launch each, one event pair
+    around all of them). Shares carry the header's index in ``job_id``."""
+    n = len(headers)
+    arr = (CHeader * n)(*[h._c() for h in headers])
+    out = (CShare * max_shares)()
+    found, hashes, launches = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
+    ms = ctypes.c_double()
+    k = check(lib().otd_scan_headers(device, arr, n, bytes(target), nonce_begin, nonce_count, variant, out,
+                                     max_shares, ctypes.byref(found), ctypes.byref(hashes), ctypes.byref(ms),
+                                     ctypes.byref(launches)))
+    did = _device_id(device)
+    return ScanResult([_share_from_c(out[i], did) for i in range(k)], found.value, hashes.value, ms.value,
+                      launches.value)
+
+
 def scan_variants() -> List[str]:
     return capi.names_list(lib().otd_scan_variants)
+
+
+def default_variant() -> int:
+    return int(lib().otd_scan_default_variant())
 
 
 # ----------------------------------------------------------------------------

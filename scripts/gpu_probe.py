@@ -16,7 +16,7 @@ out["device"] = {"model": dev.info.model.decode(), "sms": dev.info.sm_count, "cl
 print(out["device"], flush=True)
 
 peaks = {}
-for i, name in enumerate(miner.int_peak_modes()):
+for i, name in enumerate(miner.int_peak_modes() if "--no-peak" not in sys.argv else []):
     best = None
     for rep in range(3):
         ops, mhz, ms = miner.int_peak(i, iters=4096)
@@ -34,9 +34,9 @@ t = miner.target_from_nbits(W.DIFF1_NBITS)
 scan = {}
 for v, name in enumerate(miner.scan_variants()):
     rates = []
-    for rep in range(4):
+    for rep in range(3):
         r = miner.scan(miner.Work(header=hdr, target=t), variant=v)
-        assert [s.nonce for s in r.shares] == [W.GENESIS_NONCE], r.shares
+        assert [s.nonce for s in r.shares] == [2083236893, 3197545707], r.shares
         rates.append(r.hashes / (r.device_ms * 1e-3))
     scan[name] = {"ghs": [x / 1e9 for x in rates]}
     print(f"scan {name:8s} GH/s {[round(x/1e9,3) for x in rates]}", flush=True)

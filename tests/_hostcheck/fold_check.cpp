@@ -1,49 +1,73 @@
 // Host instantiation of the product's scan_core.cuh / sha256_core.cuh so the
-// constant folding and round bookkeeping can be checked on a CPU-only box
-// (tests/test_fold_host.py).  Test helper only — not shipped, not a fallback.
+// constant folding, round bookkeeping and every instruction-placement policy
+// can be checked on a CPU-only box (tests/test_fold_host.py).
+// Test helper only — not shipped, not a fallback.
 #include "../../otedama_b200/csrc/scan_core.cuh"
 using namespace otd;
 
-extern "C" {
-// e after round 60 of hash 2 via the unrolled folded path, V lanes (1,2,4).
-int fc_scan_e60(const uint8_t hdr76[76], const uint32_t* nonces, int v, uint32_t* e60_out)
+template <int V, unsigned KN>
+static void run_core(const JobConsts& jc, const uint32_t* nonces, uint32_t* out)
+{
+    vw<V> w3;
+    for (int i = 0; i < V; i++) w3.x[i] = bswap32(nonces[i]);
+    const Ops<KN> op{make_pipe_mults()};
+    vw<V> r = scan_core<V, KN>(jc, w3, op);
+    for (int i = 0; i < V; i++) out[i] = r.x[i];
+}
+template <unsigned KN>
+static int run_v(const JobConsts& jc, const uint32_t* nonces, int v, uint32_t* out)
+{
+    if (v == 1) run_core<1, KN>(jc, nonces, out);
+    else if (v == 2) run_core<2, KN>(jc, nonces, out);
+    else if (v == 4) run_core<4, KN>(jc, nonces, out);
+    else return -1;
+    return 0;
+}
+
+static void consts_for(const uint8_t hdr76[76], const uint8_t target[32], JobConsts* jc)
 {
     uint8_t hdr[80];
     memcpy(hdr, hdr76, 76);
     memset(hdr + 76, 0, 4);
     uint32_t mid[8], tail[3], tgt[8] = {0};
+    if (target)
+        for (int i = 0; i < 8; i++)
+            tgt[i] = (uint32_t)target[4 * i] | (uint32_t)target[4 * i + 1] << 8 |
+                     (uint32_t)target[4 * i + 2] << 16 | (uint32_t)target[4 * i + 3] << 24;
     header_midstate(hdr, mid, tail);
+    fold_job_consts(mid, tail[0], tail[1], tail[2], tgt, jc);
+}
+
+extern "C" {
+// e after round 60 of hash 2 via the unrolled folded path, V lanes (1, 2, 4),
+// under one of the knob sets below (the device variants use a subset of these).
+int fc_scan_e60_kn(const uint8_t hdr76[76], const uint32_t* nonces, int v, unsigned knobs, uint32_t* e60_out)
+{
     JobConsts jc;
-    fold_job_consts(mid, tail[0], tail[1], tail[2], tgt, &jc);
-    if (v == 1) {
-        vw<1> w3; w3.x[0] = bswap32(nonces[0]);
-        vw<1> r = scan_core<1>(jc, w3); e60_out[0] = r.x[0];
-    } else if (v == 2) {
-        vw<2> w3; for (int i = 0; i < 2; i++) w3.x[i] = bswap32(nonces[i]);
-        vw<2> r = scan_core<2>(jc, w3); for (int i = 0; i < 2; i++) e60_out[i] = r.x[i];
-    } else if (v == 4) {
-        vw<4> w3; for (int i = 0; i < 4; i++) w3.x[i] = bswap32(nonces[i]);
-        vw<4> r = scan_core<4>(jc, w3); for (int i = 0; i < 4; i++) e60_out[i] = r.x[i];
-    } else return -1;
-    return 0;
+    consts_for(hdr76, nullptr, &jc);
+    switch (knobs) {
+        case 0: return run_v<0>(jc, nonces, v, e60_out);
+        case 1023: return run_v<1023>(jc, nonces, v, e60_out);
+        case KN_E | KN_W1 | KN_SSHR: return run_v<KN_E | KN_W1 | KN_SSHR>(jc, nonces, v, e60_out);
+        case KN_E | KN_W1 | KN_SSHR | KN_HKW | KN_BS1:
+            return run_v<KN_E | KN_W1 | KN_SSHR | KN_HKW | KN_BS1>(jc, nonces, v, e60_out);
+        case KN_E | KN_W1 | KN_SSHR | KN_HKW | KN_BS1 | KN_BS0 | KN_SROT:
+            return run_v<KN_E | KN_W1 | KN_SSHR | KN_HKW | KN_BS1 | KN_BS0 | KN_SROT>(jc, nonces, v, e60_out);
+        case KN_T1 | KN_A | KN_W2: return run_v<KN_T1 | KN_A | KN_W2>(jc, nonces, v, e60_out);
+        default: return -2;
+    }
 }
 // Full digest through the looped midstate path (what the rare-hit path runs).
 void fc_sha256d_mid(const uint8_t hdr76[76], uint32_t nonce, const uint8_t target[32],
                     uint8_t hash_out[32], int* le_target)
 {
-    uint8_t hdr[80];
-    memcpy(hdr, hdr76, 76);
-    memset(hdr + 76, 0, 4);
-    uint32_t mid[8], tail[3], tgt[8];
-    for (int i = 0; i < 8; i++)
-        tgt[i] = (uint32_t)target[4*i] | (uint32_t)target[4*i+1] << 8 | (uint32_t)target[4*i+2] << 16 | (uint32_t)target[4*i+3] << 24;
-    header_midstate(hdr, mid, tail);
     JobConsts jc;
-    fold_job_consts(mid, tail[0], tail[1], tail[2], tgt, &jc);
+    consts_for(hdr76, target, &jc);
     uint32_t dig[8];
     sha256d_from_consts(jc, nonce, dig);
     for (int i = 0; i < 8; i++) {
-        hash_out[4*i] = dig[i] >> 24; hash_out[4*i+1] = dig[i] >> 16; hash_out[4*i+2] = dig[i] >> 8; hash_out[4*i+3] = dig[i];
+        hash_out[4 * i] = dig[i] >> 24; hash_out[4 * i + 1] = dig[i] >> 16;
+        hash_out[4 * i + 2] = dig[i] >> 8; hash_out[4 * i + 3] = dig[i];
     }
     *le_target = digest_le_target(dig, jc.target) ? 1 : 0;
 }

@@ -45,7 +45,7 @@ def full_genesis():
         "shares": [{"nonce": s.nonce, "hash": s.hash.hex()} for s in shares],
     }
     assert dropped == 0 and hashes == 1 << 32
-    assert [s.nonce for s in shares] == [2083236893], shares
+    assert 2083236893 in [s.nonce for s in shares], shares
     with open(os.path.join(HERE, "genesis_full_scan.json"), "w") as f:
         json.dump(doc, f, indent=1)
     print("genesis_full_scan.json:", doc["shares"], f"{hashes / dt / 1e6:.1f} MH/s")

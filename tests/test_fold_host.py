@@ -26,11 +26,18 @@ def fold():
     return L
 
 
-def _e60(L, h76, nonces):
+KN = dict(E=1, HKW=2, T1=4, A=8, W1=16, W2=32, SSHR=64, SROT=128, BS1=256, BS0=512)
+KNOB_SETS = [0, 1023, KN["E"] | KN["W1"] | KN["SSHR"],
+             KN["E"] | KN["W1"] | KN["SSHR"] | KN["HKW"] | KN["BS1"],
+             KN["E"] | KN["W1"] | KN["SSHR"] | KN["HKW"] | KN["BS1"] | KN["BS0"] | KN["SROT"],
+             KN["T1"] | KN["A"] | KN["W2"]]
+
+
+def _e60(L, h76, nonces, knobs=0):
     v = len(nonces)
     arr = (ctypes.c_uint32 * v)(*nonces)
     out = (ctypes.c_uint32 * v)()
-    assert L.fc_scan_e60(h76, arr, v, out) == 0
+    assert L.fc_scan_e60_kn(h76, arr, v, knobs, out) == 0
     return list(out)
 
 
@@ -44,11 +51,13 @@ def test_top_word_matches_oracle(fold, oracle):
         cases.append((rnd.randbytes(76), [rnd.getrandbits(32) for _ in range(v)]))
     cases.append((b"\x00" * 76, [0, 0xFFFFFFFF]))
     cases.append((b"\xff" * 76, [0xFFFFFFFF, 1, 2, 3]))
-    for h76, nonces in cases:
-        for n, e in zip(nonces, _e60(fold, h76, nonces)):
-            d = oracle.sha256d(h76 + struct.pack("<I", n))
-            h7 = struct.unpack(">I", d[28:32])[0]
-            assert (e + IV7) & 0xFFFFFFFF == h7
+    for ci, (h76, nonces) in enumerate(cases):
+        # every instruction-placement policy computes the same function
+        for knobs in (KNOB_SETS if ci % 8 == 0 else [KNOB_SETS[ci % len(KNOB_SETS)]]):
+            for n, e in zip(nonces, _e60(fold, h76, nonces, knobs)):
+                d = oracle.sha256d(h76 + struct.pack("<I", n))
+                h7 = struct.unpack(">I", d[28:32])[0]
+                assert (e + IV7) & 0xFFFFFFFF == h7, knobs
     # the genesis nonce is exactly the "top word zero" constant the kernel tests for
     assert _e60(fold, genesis, [2083236893])[0] == (-IV7) & 0xFFFFFFFF
 

@@ -14,6 +14,10 @@ from otedama_b200 import workloads as W
 pytestmark = pytest.mark.gpu
 
 NCPU = os.cpu_count() or 1
+# The genesis header has TWO difficulty-1 solutions in its 2^32 nonce space: the mined one and
+# 3197545707 (hash 00000000ea532922...); the CPU oracle's full scan found both
+# (tests/golden/genesis_full_scan.json).
+WANT_GENESIS_NONCES = [2083236893, 3197545707]
 
 
 @pytest.fixture(scope="module")
@@ -146,10 +150,9 @@ def test_full_nonce_range_genesis(miner, golden):
     r = miner.scan(miner.Work(header=mheader(miner, f), nbits=W.DIFF1_NBITS,
                               target=miner.target_from_nbits(W.DIFF1_NBITS)))
     assert r.hashes == 1 << 32
-    assert [(s.nonce, s.hash.hex()) for s in r.shares] == [(W.GENESIS_NONCE, W.GENESIS_HASH_HEX)]
-    g = golden.get("genesis_full_scan")
-    if g:
-        assert [(s.nonce, s.hash.hex()) for s in r.shares] == [(x["nonce"], x["hash"]) for x in g["shares"]]
+    assert (W.GENESIS_NONCE, W.GENESIS_HASH_HEX) in [(s.nonce, s.hash.hex()) for s in r.shares]
+    g = golden["genesis_full_scan"]
+    assert [(s.nonce, s.hash.hex()) for s in r.shares] == [(x["nonce"], x["hash"]) for x in g["shares"]]
 
 
 def test_config2_headers_full_range_soundness(miner, oracle):
@@ -167,6 +170,21 @@ def test_config2_headers_full_range_soundness(miner, oracle):
             assert oracle.hash_header(oh) == s.hash and oracle.less_or_equal(s.hash, t)
         total += r.found
     assert total <= 20  # Poisson mean 4
+
+
+def test_scan_headers_burst_matches_oracle(miner, oracle, golden):
+    """configs[1] shape: many headers in one burst; dense windows against the golden sets."""
+    cases = golden["synthetic_windows"]["cases"]
+    hdrs = [mheader(miner, W.config2_fields(c["index"])) for c in cases]
+    t = bytes.fromhex(cases[0]["target_hex"])
+    r = miner.scan_headers(hdrs, t, 0, 1 << 24)
+    assert r.launches == len(cases) and r.hashes == len(cases) << 24
+    for i, c in enumerate(cases):
+        mine = [s for s in r.shares if s.job_id == i]
+        assert [s.nonce for s in mine] == c["nonces"]
+        assert hashlib.sha256(b"".join(s.hash for s in mine)).hexdigest() == c["hash_digest"]
+        f = W.config2_fields(c["index"])
+        assert all(s.ntime == f["time"] and s.version == f["version"] for s in mine)
 
 
 # ------------------------------------------------- K2: BIP-320 version roll --
@@ -261,7 +279,7 @@ def test_v1_scan_with_extranonce2_matches_oracle(miner, oracle):
                                      c3["branches"])
         sh, _, _ = oracle.grind(oheader(oracle, f, merkle_root=root), t, 0xFFFF0000, 1 << 16, threads=NCPU)
         want += okey(sh, extranonce2=e)
-    assert key(r.shares) == sorted(want) and len(want) > 100
+    assert key(r.shares) == sorted(want) and len(want) > 20
     assert r.hashes == 20 << 16
 
 
@@ -384,8 +402,9 @@ def test_worker_full_range_at_difficulty_one(miner):
                               target=miner.target_from_nbits(f["bits"])))
         assert w.wait_exhausted(30000)
         sh = w.poll_shares(16, 0)
-        assert [(s.nonce, s.hash.hex(), s.job_id, s.version, s.ntime) for s in sh] == \
-               [(W.GENESIS_NONCE, W.GENESIS_HASH_HEX, 5, 1, f["time"])]
+        assert (W.GENESIS_NONCE, W.GENESIS_HASH_HEX, 5, 1, f["time"]) in \
+               [(s.nonce, s.hash.hex(), s.job_id, s.version, s.ntime) for s in sh]
+        assert sorted(s.nonce for s in sh) == WANT_GENESIS_NONCES
         st = w.stats()
         assert st.hashes_total == 1 << 32 and st.hash_rate > 1e9
 

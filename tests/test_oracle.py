@@ -146,13 +146,17 @@ def test_golden_windows_reproduce(oracle, golden):
     assert [s.nonce for s in shares] == [n for n in case["nonces"] if n < (1 << 20)]
 
 
-def test_full_genesis_scan_fixture(golden):
+def test_full_genesis_scan_fixture(golden, oracle):
     g = golden.get("genesis_full_scan")
     if g is None:
         pytest.skip("genesis_full_scan.json not generated yet")
     assert g["hashes"] == 1 << 32
-    assert [s["nonce"] for s in g["shares"]] == [2083236893]
+    # the mined nonce plus a second, never-published difficulty-1 solution
+    assert [s["nonce"] for s in g["shares"]] == [2083236893, 3197545707]
     assert g["shares"][0]["hash"] == "6fe28c0ab6f1b372c1a6a246ae63f74f931e8365e15a089c68d6190000000000"
+    for s in g["shares"]:
+        hdr = bytes.fromhex(g["header76_hex"]) + s["nonce"].to_bytes(4, "little")
+        assert oracle.sha256d_hashlib(hdr).hex() == s["hash"]
 
 
 def test_v1_merkle_root_unpinned_but_anchored(oracle, golden):
