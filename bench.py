@@ -254,11 +254,11 @@ def main():
         per_gpu_hps = value * 1e9 / world
         achieved = per_gpu_hps * ALG_OPS_PER_HASH
         roofline = {"bound": "int-issue", "achieved": achieved / 1e12, "peak": peak_alu / 1e12,
-                    "unit": "Tint-op/s", "frac": achieved / peak_alu, "traffic": 189.4,
+                    "unit": "Tint-op/s", "frac": achieved / peak_alu, "traffic": 189440,
                     "note": ("achieved = per-GPU H/s x 2450 algorithmic 3-input integer ops/hash (SURVEY §8d); "
                              "peak = measured ALU-pipe rate (SHF/LOP3/IADD3 at the SHA mix) on this GPU, of measured; "
                              "frac can exceed 1 because ptxas issues part of the adds as IMAD on the FMA pipe; "
-                             "traffic = DRAM bytes per launch from ncu (profiles/), i.e. none"),
+                             "traffic = dram__bytes_read+write (bytes) of one 2^30-candidate launch from ncu --set full (profiles/r1_ncu_scan_kernel.csv): effectively none"),
                     "peak_dual_issue": peak_dual / 1e12, "alg_ops_per_hash": ALG_OPS_PER_HASH,
                     "roofline_ghs_per_gpu": peak_alu / ALG_OPS_PER_HASH / 1e9}
         cpu = None
