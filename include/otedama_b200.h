@@ -207,6 +207,34 @@ int otd_scan_headers(int device_index, const otd_header_t* headers, uint32_t n_h
                      int kernel_variant, otd_share_t* out, uint32_t max_shares, uint64_t* n_found,
                      uint64_t* hashes, double* device_ms, uint64_t* launches);
 
+/* otd_scan_noalloc — no counterpart in the reference (Go code never deals with
+ * device memory).  It is otd_scan for callers that must not allocate: a host
+ * process whose GPU memory is owned up front by another allocator or capped by
+ * its operator, or a latency-critical caller for which cudaMalloc/cudaFree (which
+ * synchronise the whole device and can fail under memory pressure) are off
+ * limits.  The call allocates nothing on the device or the host heap: the
+ * kernel's scratch — share ring, its counters, the stop word — is a fixed
+ * OTD_NOALLOC_SCRATCH_BYTES array inside the library that every GPU loading it
+ * holds until the process exits.
+ *   - Plain-header work only (no version rolling, no coinbase); the nonce window
+ *     may be anything up to 2^32.
+ *   - max_shares may not exceed OTD_NOALLOC_MAX_SHARES (the ring's size): a larger
+ *     request fails with OTD_ERANGE.  More shares than max_shares found on the
+ *     device are dropped and show up in *n_found.
+ *   - The first call on a device looks up the array's device address; make that
+ *     first call before starting any CUDA stream capture.
+ *   - All calls share the one array and it keeps the previous call's contents;
+ *     each call clears the counters it needs.  The call is synchronous and the
+ *     library lets only one run at a time — two scans using the array at once on
+ *     the GPU would race, so do not try to overlap them from outside either
+ *     (another process gets its own copy of the array).
+ * Output is the same as otd_scan's for the same work (sorted by nonce); returns
+ * the number of shares written. */
+#define OTD_NOALLOC_MAX_SHARES 4096u
+#define OTD_NOALLOC_SCRATCH_BYTES (256u + 40u * OTD_NOALLOC_MAX_SHARES) /* 164,096 bytes per GPU */
+int otd_scan_noalloc(int device_index, const otd_work_t* work, int kernel_variant, otd_share_t* out,
+                     uint32_t max_shares, uint64_t* n_found, uint64_t* hashes);
+
 /* Kernel variants compiled into the library: returns the count, fills
  * names[i] (each up to 32 bytes incl. NUL) when names != NULL. */
 int otd_scan_variants(char (*names)[32], int max_names);

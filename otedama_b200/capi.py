@@ -18,6 +18,7 @@ HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "otedama_b200.h")
 
 OTD_OK, OTD_EINVAL, OTD_ENODEV, OTD_ENOMEM, OTD_EBUSY, OTD_ECUDA, OTD_ERANGE = 0, -22, -19, -12, -16, -5, -34
 OTD_WORK_REPEAT = 1
+OTD_NOALLOC_MAX_SHARES = 4096
 
 
 class OtdError(RuntimeError):
@@ -97,6 +98,8 @@ _SIGS = {
     "otd_scan_headers": (c_int, [c_int, POINTER(CHeader), c_uint32, c_char_p, c_uint32, c_uint64, c_int,
                                  POINTER(CShare), c_uint32, POINTER(c_uint64), POINTER(c_uint64),
                                  POINTER(c_double), POINTER(c_uint64)]),
+    "otd_scan_noalloc": (c_int, [c_int, POINTER(CWork), c_int, POINTER(CShare), c_uint32, POINTER(c_uint64),
+                                 POINTER(c_uint64)]),
     "otd_scan_variants": (c_int, [c_void_p, c_int]),
     "otd_scan_default_variant": (c_int, []),
     "otd_prepare_instances": (c_int, [c_int, POINTER(CWork), c_uint32, c_uint32, c_char_p,

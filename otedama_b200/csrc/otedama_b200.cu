@@ -1125,3 +1125,112 @@ extern "C" int otd_int_peak(int device_index, int mode, int iters, double* ops_p
     if (ms_out) *ms_out = ms;
     return OTD_OK;
 }
+
+// ----------------------------------------------------- scan without allocation --
+// otd_scan_noalloc: the same search as otd_scan for a plain-header work, for
+// callers that are not allowed to (or cannot) allocate device memory — a process
+// whose GPU memory is handed out up front by another allocator or capped by its
+// operator, or code on a latency-critical path, where cudaMalloc/cudaFree would
+// synchronise the whole device or fail under memory pressure.  Nothing is
+// allocated here, on the device or the host heap: the kernel's scratch (share
+// ring, its counters, the stop word) lives in ONE file-scope device array that
+// every GPU loading this library holds until the process exits.
+//
+// Layout of the array: [0,16) ring header (count / candidates / blocks_done),
+// [64,68) stop word, [256, 256 + 40*OTD_NOALLOC_MAX_SHARES) ring entries.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[OTD_NOALLOC_SCRATCH_BYTES];
+
+static_assert(sizeof(RingEntry) == 40 && sizeof(RingHeader) == 16, "scratch layout");
+static_assert(256 + sizeof(RingEntry) * OTD_NOALLOC_MAX_SHARES <= OTD_NOALLOC_SCRATCH_BYTES, "scratch size");
+
+static const int kNoallocMaxDevices = 64;
+static std::mutex g_noalloc_mu;                               // one call at a time: every call shares the array
+static unsigned char* g_noalloc_ptr[kNoallocMaxDevices];      // device address of the array, per device
+static bool g_noalloc_ready[kNoallocMaxDevices];
+
+// Set-up, once per device, with that device current.  In host code the name
+// g_noalloc_scratch is only a handle for the symbol, not a device address: the
+// kernel must be given what cudaGetSymbolAddress returns.
+static int noalloc_setup(int dev, unsigned char** out)
+{
+    if (dev < 0 || dev >= kNoallocMaxDevices) return fail(OTD_EINVAL, "otd_scan_noalloc: device index out of range");
+    if (!g_noalloc_ready[dev]) {
+        unsigned char* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr)
+            return fail(OTD_ECUDA, std::string("otd_scan_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+        g_noalloc_ptr[dev] = p;
+        g_noalloc_ready[dev] = true;
+    }
+    *out = g_noalloc_ptr[dev];
+    return OTD_OK;
+}
+
+extern "C" int otd_scan_noalloc(int device_index, const otd_work_t* work, int kernel_variant, otd_share_t* out,
+                                uint32_t max_shares, uint64_t* n_found, uint64_t* hashes)
+{
+    if (!work) return fail(OTD_EINVAL, "otd_scan_noalloc: work is NULL");
+    if (max_shares && !out) return fail(OTD_EINVAL, "otd_scan_noalloc: out is NULL");
+    if (max_shares > OTD_NOALLOC_MAX_SHARES)
+        return fail(OTD_ERANGE, "otd_scan_noalloc: max_shares " + std::to_string(max_shares) +
+                                    " exceeds the fixed ring of " + std::to_string(OTD_NOALLOC_MAX_SHARES) +
+                                    " entries (use otd_scan for larger result sets)");
+    if (work->version_mask || work->coinb1 || work->version_count > 1)
+        return fail(OTD_EINVAL, "otd_scan_noalloc: only plain-header work (no version rolling, no coinbase) is supported");
+    const uint64_t nonce_count = work->nonce_count ? work->nonce_count : (1ull << 32);
+    if ((uint64_t)work->nonce_begin + nonce_count > (1ull << 32))
+        return fail(OTD_EINVAL, "nonce window exceeds 2^32");
+    int rc = check_device(device_index);
+    if (rc) return rc;
+    if (kernel_variant < 0 || kernel_variant >= kNumVariants) kernel_variant = kDefaultVariant;
+    const ScanVariant& kv = kVariants[kernel_variant];
+
+    std::lock_guard<std::mutex> g(g_noalloc_mu);
+    CU_TRY(cudaSetDevice(device_index));
+    unsigned char* base = nullptr;
+    if ((rc = noalloc_setup(device_index, &base))) return rc;
+    RingHeader* d_hdr = reinterpret_cast<RingHeader*>(base);
+    unsigned int* d_stop = reinterpret_cast<unsigned int*>(base + 64);
+    RingEntry* d_ent = reinterpret_cast<RingEntry*>(base + 256);
+    const uint32_t cap = max_shares;  // entries beyond the caller's buffer would be dropped anyway
+
+    // job constants on the host stack (midstate + folding), as for any plain header
+    uint8_t hdr[80];
+    uint32_t mid[8], tail[3], tgt[8];
+    otd_header_bytes(&work->header, hdr);
+    header_midstate(hdr, mid, tail);
+    for (int i = 0; i < 8; i++) tgt[i] = get_le32(work->target + 4 * i);
+    JobConsts jc;
+    fold_job_consts(mid, tail[0], tail[1], tail[2], tgt, &jc);
+
+    // The array keeps the previous call's contents: the counters and the stop word must
+    // start at zero (generation 0 = "keep running"); ring entries need no clearing, only
+    // the first `count` of them are ever read back.
+    CU_TRY(cudaMemset(base, 0, 256));
+    cudaError_t le = kv.fn(jc, work->nonce_begin, nonce_count, 0u, d_hdr, d_ent, cap, d_stop, 0u, (cudaStream_t)0);
+    if (le != cudaSuccess) return fail(OTD_ECUDA, std::string("otd_scan_noalloc: launch: ") + cudaGetErrorString(le));
+    RingHeader h;
+    CU_TRY(cudaMemcpy(&h, d_hdr, sizeof h, cudaMemcpyDeviceToHost));  // waits for the kernel
+    const uint32_t n = std::min(h.count, cap);
+    RingEntry chunk[128];
+    for (uint32_t done = 0; done < n; done += 128) {
+        const uint32_t m = std::min<uint32_t>(128, n - done);
+        CU_TRY(cudaMemcpy(chunk, d_ent + done, sizeof(RingEntry) * m, cudaMemcpyDeviceToHost));
+        for (uint32_t i = 0; i < m; i++) {
+            otd_share_t& sh = out[done + i];
+            memset(&sh, 0, sizeof sh);
+            sh.channel_id = work->channel_id;
+            sh.job_id = work->job_id;
+            sh.nonce = chunk[i].nonce;
+            sh.ntime = work->header.time;
+            sh.version = work->header.version;
+            memcpy(sh.hash, chunk[i].hash, 32);
+            sh.work_seq = 1;
+            sh.device_index = device_index;
+        }
+    }
+    std::sort(out, out + n, [](const otd_share_t& a, const otd_share_t& b) { return a.nonce < b.nonce; });
+    if (n_found) *n_found = h.count;
+    if (hashes) *hashes = nonce_count;
+    return (int)n;
+}
