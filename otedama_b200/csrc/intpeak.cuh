@@ -22,7 +22,11 @@ enum IntPeakMode {
     IPM_PRMT = 8,      // prmt chains                                   (ALU pipe)
     IPM_ALU_FMA = 9,   // 1 LOP3 : 1 IMAD interleaved                   (both pipes)
     IPM_IMAD_HI = 10,  // mul.hi.u32 with a runtime multiplier          (FMA pipe)
-    IPM_COUNT = 11
+    IPM_ALU_WIDE = 11,   // 1 LOP3 : 1 IMAD.WIDE                         (both pipes)
+    IPM_ALU2_WIDE = 12,  // 1 SHF + 1 LOP3 : 1 IMAD.WIDE                 (both pipes)
+    IPM_ALU2_FMA = 13,   // 1 SHF + 1 LOP3 : 1 IMAD                      (both pipes)
+    IPM_ALU_WIDE_FMA = 14, // 2 ALU : 1 IMAD.WIDE : 1 IMAD               (the balanced SHA mix)
+    IPM_COUNT = 15
 };
 
 #if defined(__CUDACC__)
@@ -34,7 +38,9 @@ constexpr int kIpUnroll = 16;
 __host__ __device__ constexpr int ip_ops_per_step(int mode)
 {
     return (mode == IPM_MIX_ALU || mode == IPM_MIX_DUAL || mode == IPM_MIX_DUAL1) ? 4
-           : (mode == IPM_ALU_FMA)                                                ? 2
+           : (mode == IPM_ALU_FMA || mode == IPM_ALU_WIDE)                        ? 2
+           : (mode == IPM_ALU2_WIDE || mode == IPM_ALU2_FMA)                      ? 3
+           : (mode == IPM_ALU_WIDE_FMA)                                           ? 4
                                                                                   : 1;
 }
 
@@ -101,6 +107,25 @@ __global__ void __launch_bounds__(1024) int_peak_kernel(int iters, uint32_t one,
                     asm volatile("prmt.b32 %0, %0, %1, 0x0321;" : "+r"(x[c]) : "r"(y[c]));
                 } else if (MODE == IPM_IMAD_HI) {
                     asm volatile("mul.hi.u32 %0, %0, %1;" : "+r"(x[c]) : "r"(seed));
+                } else if (MODE == IPM_ALU_WIDE) {
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("{ .reg .u64 w;\n mul.wide.u32 w, %0, %2;\n mov.b64 {%0, %1}, w; }"
+                                 : "+r"(y[c]), "=r"(z[c]) : "r"(one));
+                } else if (MODE == IPM_ALU2_WIDE) {
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("{ .reg .u64 w;\n mul.wide.u32 w, %0, %2;\n mov.b64 {%0, %1}, w; }"
+                                 : "+r"(y[c]), "=r"(z[c]) : "r"(one));
+                } else if (MODE == IPM_ALU2_FMA) {
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(z[c]));
+                } else if (MODE == IPM_ALU_WIDE_FMA) {
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
+                    asm volatile("{ .reg .u64 w;\n mul.wide.u32 w, %0, %2;\n mov.b64 {%0, %1}, w; }"
+                                 : "+r"(y[c]), "=r"(z[c]) : "r"(one));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(x[c]));
                 } else if (MODE == IPM_ALU_FMA) {
                     asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
                     asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(z[c]));

@@ -15,6 +15,7 @@
 #include <cmath>
 #include <condition_variable>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <functional>
@@ -303,13 +304,27 @@ struct ScanVariant {
     const char* name;
     int v, iter;
     unsigned knobs;
+    bool half;  // experiment: stops after hash 1, does not compute SHA-256d
     otd_scan_launch_fn fn;
 };
-#define OTD_TABLE_ROW(idx, name, v, iter, kn) {name, v, iter, kn, otd_scan_launch_##idx},
-static const ScanVariant kVariants[] = {OTD_SCAN_VARIANTS(OTD_TABLE_ROW)};
+#define OTD_TABLE_ROW(idx, name, v, iter, kn, half, minb) {name, v, iter, kn, half, otd_scan_launch_##idx},
+static const ScanVariant kAllVariants[] = {OTD_SCAN_VARIANTS(OTD_TABLE_ROW)};
 #undef OTD_TABLE_ROW
-static const int kNumVariants = (int)(sizeof kVariants / sizeof kVariants[0]);
+static const int kNumAllVariants = (int)(sizeof kAllVariants / sizeof kAllVariants[0]);
 static const int kDefaultVariant = OTD_DEFAULT_VARIANT;
+static const ScanVariant* const kVariants = kAllVariants;
+
+// Production variants are [0, OTD_NUM_PRODUCTION_VARIANTS); the experimental ones behind
+// them are reachable by index only when OTD_ALLOW_EXPERIMENTAL=1 (performance studies).
+static int num_usable_variants()
+{
+    static const int n = [] {
+        const char* e = getenv("OTD_ALLOW_EXPERIMENTAL");
+        return (e && e[0] == '1') ? kNumAllVariants : OTD_NUM_PRODUCTION_VARIANTS;
+    }();
+    return n;
+}
+#define kNumVariants (num_usable_variants())
 
 extern "C" int otd_scan_variants(char (*names)[32], int max_names)
 {
@@ -1067,7 +1082,8 @@ extern "C" int otd_worker_destroy(otd_worker_t* w)
 
 // ---------------------------------------------------------------- int peak --
 static const char* kIntPeakNames[IPM_COUNT] = {"lop3", "shf", "iadd3", "imad", "mix_alu",
-                                               "mix_dual", "mix_dual1", "imad_wide", "prmt", "alu_fma", "imad_hi"};
+                                               "mix_dual", "mix_dual1", "imad_wide", "prmt", "alu_fma", "imad_hi",
+                                               "alu_wide", "alu2_wide", "alu2_fma", "alu_wide_fma"};
 
 extern "C" int otd_int_peak_modes(char (*names)[32], int max_names)
 {
@@ -1106,7 +1122,8 @@ extern "C" int otd_int_peak(int device_index, int mode, int iters, double* ops_p
     CU_TRY(cudaEventCreate(&e1));
     typedef cudaError_t (*fn_t)(int, int, uint32_t*, long long*, cudaStream_t);
     static const fn_t fns[IPM_COUNT] = {launch_peak<0>, launch_peak<1>, launch_peak<2>, launch_peak<3>, launch_peak<4>,
-                                        launch_peak<5>, launch_peak<6>, launch_peak<7>, launch_peak<8>, launch_peak<9>, launch_peak<10>};
+                                        launch_peak<5>, launch_peak<6>, launch_peak<7>, launch_peak<8>, launch_peak<9>, launch_peak<10>,
+                                        launch_peak<11>, launch_peak<12>, launch_peak<13>, launch_peak<14>};
     cudaError_t e = cudaSuccess;
     for (int w = 0; w < 2 && e == cudaSuccess; w++) e = fns[mode](grid, iters / 4 + 1, d_sink, d_cyc, st);  // warm-up
     float ms = 0;

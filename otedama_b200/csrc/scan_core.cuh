@@ -100,6 +100,9 @@ enum : unsigned {
     KN_SROT = 128u,  // sigma0/1: both rotations    via IMAD.WIDE
     KN_BS1 = 256u,   // Sigma1: two of three rotations via IMAD.WIDE
     KN_BS0 = 512u,   // Sigma0: two of three rotations via IMAD.WIDE
+    KN_T1X = 1024u,  // t1 = IMAD(IADD3(IMAD(h,1,W), Sigma1, K), 1, Ch): one ALU add, no IMAD with an immediate
+    KN_COMPACT = 2048u,  // partially rolled body (scan_core_compact): the three fully generic 16-round blocks
+                         // share one loop body so the code stays well inside the instruction cache
 };
 
 struct PipeMults {  // run-time constants the compiler cannot fold (kernel parameter)
@@ -205,51 +208,70 @@ struct Ops {
         const uint32_t t = add3_if(KN & KN_W2, s1(w2), w7, s0(w15));
         return add_if(KN & KN_W1, t, w16);
     }
-    // one round on scalars; kw = K + W already summed (or an immediate)
-    OTD_HD void round(uint32_t a, uint32_t b, uint32_t c, uint32_t& d, uint32_t e, uint32_t f, uint32_t g,
-                      uint32_t& h, uint32_t kw) const
+    // t1 = h + Sigma1(e) + Ch(e,f,g) + K + W  (W a per-candidate word)
+    OTD_HD uint32_t t1_kw(uint32_t h, uint32_t e, uint32_t f, uint32_t g, uint32_t w, uint32_t k) const
     {
+        if (KN & KN_T1X) {
+            const uint32_t x = fma_add(h, w, m.one);
+            const uint32_t y = x + S1(e) + k;
+            return fma_add(y, ch(e, f, g), m.one);
+        }
+        const uint32_t kw = add_if(KN & KN_HKW, w, k);
         const uint32_t hk = add_if(KN & KN_HKW, h, kw);
-        const uint32_t t1 = add3_if(KN & KN_T1, hk, S1(e), ch(e, f, g));
+        return add3_if(KN & KN_T1, hk, S1(e), ch(e, f, g));
+    }
+    // same with K + W a job constant or an immediate
+    OTD_HD uint32_t t1_k(uint32_t h, uint32_t e, uint32_t f, uint32_t g, uint32_t k) const
+    {
+        if (KN & KN_T1X) {
+            const uint32_t y = h + S1(e) + k;
+            return fma_add(y, ch(e, f, g), m.one);
+        }
+        const uint32_t hk = h + k;
+        return add3_if(KN & KN_T1, hk, S1(e), ch(e, f, g));
+    }
+    OTD_HD void finish(uint32_t t1, uint32_t a, uint32_t b, uint32_t c, uint32_t& d, uint32_t& h) const
+    {
         d = add_if(KN & KN_E, d, t1);
         h = add3_if(KN & KN_A, t1, S0(a), maj(a, b, c));
     }
-    // K + W (W per-candidate): IMAD when h+K+W is split onto the FMA pipe
-    OTD_HD uint32_t kplus(uint32_t w, uint32_t k) const { return add_if(KN & KN_HKW, w, k); }
 };
 
 // ---- vector wrappers over Ops -------------------------------------------------
-template <int V> OTD_HD uint32_t lane(const vw<V>& x, int i) { return x.x[i]; }
-template <int V> OTD_HD uint32_t lane(uint32_t x, int) { return x; }
-
-// One full round.  On return d holds the new e and h holds the new a; callers
-// rotate the argument order instead of moving registers.
-template <int V, unsigned KN, typename KW>
+// One full round with a per-candidate message word w and round constant k.  On
+// return d holds the new e and h holds the new a; callers rotate the argument
+// order instead of moving registers.
+template <int V, unsigned KN>
 OTD_HD void rnd(const Ops<KN>& op, const vw<V>& a, const vw<V>& b, const vw<V>& c, vw<V>& d, const vw<V>& e,
-                const vw<V>& f, const vw<V>& g, vw<V>& h, const KW& kw)
+                const vw<V>& f, const vw<V>& g, vw<V>& h, const vw<V>& w, uint32_t k)
 {
 #pragma unroll
-    for (int i = 0; i < V; i++) op.round(a.x[i], b.x[i], c.x[i], d.x[i], e.x[i], f.x[i], g.x[i], h.x[i], lane<V>(kw, i));
+    for (int i = 0; i < V; i++) {
+        const uint32_t t1 = op.t1_kw(h.x[i], e.x[i], f.x[i], g.x[i], w.x[i], k);
+        op.finish(t1, a.x[i], b.x[i], c.x[i], d.x[i], h.x[i]);
+    }
+}
+// ... with K + W a job constant or an immediate
+template <int V, unsigned KN>
+OTD_HD void rnd(const Ops<KN>& op, const vw<V>& a, const vw<V>& b, const vw<V>& c, vw<V>& d, const vw<V>& e,
+                const vw<V>& f, const vw<V>& g, vw<V>& h, uint32_t kw)
+{
+#pragma unroll
+    for (int i = 0; i < V; i++) {
+        const uint32_t t1 = op.t1_k(h.x[i], e.x[i], f.x[i], g.x[i], kw);
+        op.finish(t1, a.x[i], b.x[i], c.x[i], d.x[i], h.x[i]);
+    }
 }
 // e-chain only (the a value produced here is never consumed).
 template <int V, unsigned KN>
 OTD_HD void rnd_e(const Ops<KN>& op, vw<V>& d, const vw<V>& e, const vw<V>& f, const vw<V>& g, const vw<V>& h,
-                  const vw<V>& kw)
+                  const vw<V>& w, uint32_t k)
 {
 #pragma unroll
     for (int i = 0; i < V; i++) {
-        const uint32_t hk = op.add_if(KN & KN_HKW, h.x[i], kw.x[i]);
-        const uint32_t t1 = op.add3_if(KN & KN_T1, hk, op.S1(e.x[i]), ch(e.x[i], f.x[i], g.x[i]));
+        const uint32_t t1 = op.t1_kw(h.x[i], e.x[i], f.x[i], g.x[i], w.x[i], k);
         d.x[i] = op.add_if(KN & KN_E, d.x[i], t1);
     }
-}
-template <int V, unsigned KN>
-OTD_HD vw<V> kpl(const Ops<KN>& op, const vw<V>& w, uint32_t k)
-{
-    vw<V> r;
-#pragma unroll
-    for (int i = 0; i < V; i++) r.x[i] = op.kplus(w.x[i], k);
-    return r;
 }
 template <int V, unsigned KN>
 OTD_HD vw<V> sched(const Ops<KN>& op, const vw<V>& w2, const vw<V>& w7, const vw<V>& w15, const vw<V>& w16)
@@ -290,18 +312,21 @@ template <int V, unsigned KN> OTD_HD vw<V> vS1(const Ops<KN>& op, const vw<V>& x
 
 // 8 rounds starting at round index R with schedule words w[R..R+7] already final.
 #define OTD_R8(R, a, b, c, d, e, f, g, h)                                \
-    rnd(op, a, b, c, d, e, f, g, h, kpl(op, w[(R) + 0], Kc((R) + 0)));   \
-    rnd(op, h, a, b, c, d, e, f, g, kpl(op, w[(R) + 1], Kc((R) + 1)));   \
-    rnd(op, g, h, a, b, c, d, e, f, kpl(op, w[(R) + 2], Kc((R) + 2)));   \
-    rnd(op, f, g, h, a, b, c, d, e, kpl(op, w[(R) + 3], Kc((R) + 3)));   \
-    rnd(op, e, f, g, h, a, b, c, d, kpl(op, w[(R) + 4], Kc((R) + 4)));   \
-    rnd(op, d, e, f, g, h, a, b, c, kpl(op, w[(R) + 5], Kc((R) + 5)));   \
-    rnd(op, c, d, e, f, g, h, a, b, kpl(op, w[(R) + 6], Kc((R) + 6)));   \
-    rnd(op, b, c, d, e, f, g, h, a, kpl(op, w[(R) + 7], Kc((R) + 7)));
+    rnd(op, a, b, c, d, e, f, g, h, w[(R) + 0], Kc((R) + 0));   \
+    rnd(op, h, a, b, c, d, e, f, g, w[(R) + 1], Kc((R) + 1));   \
+    rnd(op, g, h, a, b, c, d, e, f, w[(R) + 2], Kc((R) + 2));   \
+    rnd(op, f, g, h, a, b, c, d, e, w[(R) + 3], Kc((R) + 3));   \
+    rnd(op, e, f, g, h, a, b, c, d, w[(R) + 4], Kc((R) + 4));   \
+    rnd(op, d, e, f, g, h, a, b, c, w[(R) + 5], Kc((R) + 5));   \
+    rnd(op, c, d, e, f, g, h, a, b, w[(R) + 6], Kc((R) + 6));   \
+    rnd(op, b, c, d, e, f, g, h, a, w[(R) + 7], Kc((R) + 7));
 
 // Returns e after round 60 of the second hash for V candidates whose block-2
 // word 3 (the big-endian nonce word) is w3.  Digest word 7 = IV7 + result.
-template <int V, unsigned KN>
+// HALF (performance experiments only, never shipped as a scan variant's result):
+// stop after hash 1 and return its digest word 7 minus IV7, so that instruction
+// placement can be studied on a body that fits the instruction cache.
+template <int V, unsigned KN, bool HALF = false>
 OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
 {
     vw<V> w[64];
@@ -359,26 +384,28 @@ OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
 
     rnd(op, h, a, b, c, d, e, f, g, jc.kw16);
     rnd(op, g, h, a, b, c, d, e, f, jc.kw17);
-    rnd(op, f, g, h, a, b, c, d, e, kpl(op, w[18], Kc(18)));
-    rnd(op, e, f, g, h, a, b, c, d, kpl(op, w[19], Kc(19)));
-    rnd(op, d, e, f, g, h, a, b, c, kpl(op, w[20], Kc(20)));
-    rnd(op, c, d, e, f, g, h, a, b, kpl(op, w[21], Kc(21)));
-    rnd(op, b, c, d, e, f, g, h, a, kpl(op, w[22], Kc(22)));
-    rnd(op, a, b, c, d, e, f, g, h, kpl(op, w[23], Kc(23)));
-    rnd(op, h, a, b, c, d, e, f, g, kpl(op, w[24], Kc(24)));
-    rnd(op, g, h, a, b, c, d, e, f, kpl(op, w[25], Kc(25)));
-    rnd(op, f, g, h, a, b, c, d, e, kpl(op, w[26], Kc(26)));
-    rnd(op, e, f, g, h, a, b, c, d, kpl(op, w[27], Kc(27)));
-    rnd(op, d, e, f, g, h, a, b, c, kpl(op, w[28], Kc(28)));
-    rnd(op, c, d, e, f, g, h, a, b, kpl(op, w[29], Kc(29)));
-    rnd(op, b, c, d, e, f, g, h, a, kpl(op, w[30], Kc(30)));
-    rnd(op, a, b, c, d, e, f, g, h, kpl(op, w[31], Kc(31)));
+    rnd(op, f, g, h, a, b, c, d, e, w[18], Kc(18));
+    rnd(op, e, f, g, h, a, b, c, d, w[19], Kc(19));
+    rnd(op, d, e, f, g, h, a, b, c, w[20], Kc(20));
+    rnd(op, c, d, e, f, g, h, a, b, w[21], Kc(21));
+    rnd(op, b, c, d, e, f, g, h, a, w[22], Kc(22));
+    rnd(op, a, b, c, d, e, f, g, h, w[23], Kc(23));
+    rnd(op, h, a, b, c, d, e, f, g, w[24], Kc(24));
+    rnd(op, g, h, a, b, c, d, e, f, w[25], Kc(25));
+    rnd(op, f, g, h, a, b, c, d, e, w[26], Kc(26));
+    rnd(op, e, f, g, h, a, b, c, d, w[27], Kc(27));
+    rnd(op, d, e, f, g, h, a, b, c, w[28], Kc(28));
+    rnd(op, c, d, e, f, g, h, a, b, w[29], Kc(29));
+    rnd(op, b, c, d, e, f, g, h, a, w[30], Kc(30));
+    rnd(op, a, b, c, d, e, f, g, h, w[31], Kc(31));
     // after round 31 the "a" role is back on register h
     OTD_R8(32, h, a, b, c, d, e, f, g)
     OTD_R8(40, h, a, b, c, d, e, f, g)
     OTD_R8(48, h, a, b, c, d, e, f, g)
     OTD_R8(56, h, a, b, c, d, e, f, g)
     // the role order now is (h,a,b,c,d,e,f,g) = (A,B,C,D,E,F,G,H).
+
+    if (HALF) return g + (jc.mid[7] - IV7);
 
     // ---------------- hash 2 ----------------
     // message = digest of hash 1 (state + midstate), padding, length 256 bits
@@ -409,15 +436,15 @@ OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
     // rounds 0..3 still see compile-time constants (IV words) in the state: plain C so they fold
     {
         const Ops<0> fold{};
-        rnd(fold, a, b, c, d, e, f, g, h, w[0] + Kc(0));
-        rnd(fold, h, a, b, c, d, e, f, g, w[1] + Kc(1));
-        rnd(fold, g, h, a, b, c, d, e, f, w[2] + Kc(2));
-        rnd(fold, f, g, h, a, b, c, d, e, w[3] + Kc(3));
+        rnd(fold, a, b, c, d, e, f, g, h, w[0], Kc(0));
+        rnd(fold, h, a, b, c, d, e, f, g, w[1], Kc(1));
+        rnd(fold, g, h, a, b, c, d, e, f, w[2], Kc(2));
+        rnd(fold, f, g, h, a, b, c, d, e, w[3], Kc(3));
     }
-    rnd(op, e, f, g, h, a, b, c, d, kpl(op, w[4], Kc(4)));
-    rnd(op, d, e, f, g, h, a, b, c, kpl(op, w[5], Kc(5)));
-    rnd(op, c, d, e, f, g, h, a, b, kpl(op, w[6], Kc(6)));
-    rnd(op, b, c, d, e, f, g, h, a, kpl(op, w[7], Kc(7)));
+    rnd(op, e, f, g, h, a, b, c, d, w[4], Kc(4));
+    rnd(op, d, e, f, g, h, a, b, c, w[5], Kc(5));
+    rnd(op, c, d, e, f, g, h, a, b, w[6], Kc(6));
+    rnd(op, b, c, d, e, f, g, h, a, w[7], Kc(7));
     rnd(op, a, b, c, d, e, f, g, h, Kc(8) + 0x80000000u);
     rnd(op, h, a, b, c, d, e, f, g, Kc(9));
     rnd(op, g, h, a, b, c, d, e, f, Kc(10));
@@ -432,13 +459,208 @@ OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
     OTD_R8(40, a, b, c, d, e, f, g, h)
     OTD_R8(48, a, b, c, d, e, f, g, h)
     // round 56 full, rounds 57..60 e-chain only
-    rnd(op, a, b, c, d, e, f, g, h, kpl(op, w[56], Kc(56)));
-    rnd_e(op, c, d, e, f, g, kpl(op, w[57], Kc(57)));
-    rnd_e(op, b, c, d, e, f, kpl(op, w[58], Kc(58)));
-    rnd_e(op, a, b, c, d, e, kpl(op, w[59], Kc(59)));
-    rnd_e(op, h, a, b, c, d, kpl(op, w[60], Kc(60)));
+    rnd(op, a, b, c, d, e, f, g, h, w[56], Kc(56));
+    rnd_e(op, c, d, e, f, g, w[57], Kc(57));
+    rnd_e(op, b, c, d, e, f, w[58], Kc(58));
+    rnd_e(op, a, b, c, d, e, w[59], Kc(59));
+    rnd_e(op, h, a, b, c, d, w[60], Kc(60));
     return h;
 }
+
+// ---------------------------------------------------------------------------
+// Compact form.  Same arithmetic as scan_core, but the three 16-round blocks
+// whose message schedule is fully generic (hash 1 rounds 32..47 and 48..63, hash 2
+// rounds 32..47) run through ONE loop body with the round constants fetched from
+// the constant table, and the two hashes are the two trips of an outer loop so
+// that body exists once in the code.  Everything with folding opportunities
+// (first 32 rounds of each hash, the e-chain tail) stays specialised and
+// unrolled.  The fully unrolled scan_core is ~50 KB of SASS, right at the edge of
+// what the SM's instruction cache sustains with 40 warps at different PCs; this
+// form is ~35 KB and leaves room for the extra IMADs of the add-offload policies.
+// ---------------------------------------------------------------------------
+template <int V, unsigned KN>
+OTD_HD void generic16(const Ops<KN>& op, vw<V> (&w)[16], vw<V>& a, vw<V>& b, vw<V>& c, vw<V>& d, vw<V>& e,
+                      vw<V>& f, vw<V>& g, vw<V>& h, int kbase)
+{
+    uint32_t k[16];
+#pragma unroll
+    for (int r = 0; r < 16; r++) k[r] = Kr(kbase + r);
+#define OTD_GEN_W(r) w[r] = sched(op, w[((r) + 14) & 15], w[((r) + 9) & 15], w[((r) + 1) & 15], w[r])
+#define OTD_GEN8(R)                                                   \
+    OTD_GEN_W((R) + 0); rnd(op, a, b, c, d, e, f, g, h, w[(R) + 0], k[(R) + 0]); \
+    OTD_GEN_W((R) + 1); rnd(op, h, a, b, c, d, e, f, g, w[(R) + 1], k[(R) + 1]); \
+    OTD_GEN_W((R) + 2); rnd(op, g, h, a, b, c, d, e, f, w[(R) + 2], k[(R) + 2]); \
+    OTD_GEN_W((R) + 3); rnd(op, f, g, h, a, b, c, d, e, w[(R) + 3], k[(R) + 3]); \
+    OTD_GEN_W((R) + 4); rnd(op, e, f, g, h, a, b, c, d, w[(R) + 4], k[(R) + 4]); \
+    OTD_GEN_W((R) + 5); rnd(op, d, e, f, g, h, a, b, c, w[(R) + 5], k[(R) + 5]); \
+    OTD_GEN_W((R) + 6); rnd(op, c, d, e, f, g, h, a, b, w[(R) + 6], k[(R) + 6]); \
+    OTD_GEN_W((R) + 7); rnd(op, b, c, d, e, f, g, h, a, w[(R) + 7], k[(R) + 7]);
+    OTD_GEN8(0)
+    OTD_GEN8(8)
+#undef OTD_GEN8
+}
+
+template <int V, unsigned KN>
+OTD_HD vw<V> scan_core_compact(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
+{
+    vw<V> w[16];                  // rolling window: W[i] lives in w[i & 15]
+    vw<V> a, b, c, d, e, f, g, h; // roles (A..H) at every loop boundary
+    vw<V> result = bc<V>(0u);
+#pragma unroll 1
+    for (int phase = 0; phase < 2; phase++) {
+        if (phase == 0) {
+            // ---------------- hash 1, block 2, rounds 3..31 ----------------
+            vw<V> x[32];  // W16..W31 as named values
+            a = w3 + jc.ca3;      b = bc<V>(jc.a3); c = bc<V>(jc.b3); d = bc<V>(jc.c3);
+            e = w3 + jc.ce3;      f = bc<V>(jc.e3); g = bc<V>(jc.f3); h = bc<V>(jc.g3);
+            {
+                vw<V> t1 = vS1(op, e) + ch(e, f, g) + jc.k4;                  // round 4
+                vw<V> e5 = t1 + jc.c3;
+                vw<V> a5 = t1 + vS0(op, a) + maj(a, b, c);
+                t1 = vS1(op, e5) + ch(e5, e, f) + jc.k5;                      // round 5
+                vw<V> e6 = t1 + jc.b3;
+                vw<V> a6 = t1 + vS0(op, a5) + maj(a5, a, b);
+                t1 = vS1(op, e6) + ch(e6, e5, e) + jc.k6;                     // round 6
+                vw<V> e7 = t1 + jc.a3;
+                vw<V> a7 = t1 + vS0(op, a6) + maj(a6, a5, a);
+                vw<V> a4 = a, e4 = e;
+                a = a7; b = a6; c = a5; d = a4; e = e7; f = e6; g = e5; h = e4;
+            }
+            rnd(op, a, b, c, d, e, f, g, h, Kc(7));
+            rnd(op, h, a, b, c, d, e, f, g, Kc(8));
+            rnd(op, g, h, a, b, c, d, e, f, Kc(9));
+            rnd(op, f, g, h, a, b, c, d, e, Kc(10));
+            rnd(op, e, f, g, h, a, b, c, d, Kc(11));
+            rnd(op, d, e, f, g, h, a, b, c, Kc(12));
+            rnd(op, c, d, e, f, g, h, a, b, Kc(13));
+            rnd(op, b, c, d, e, f, g, h, a, Kc(14));
+            rnd(op, a, b, c, d, e, f, g, h, Kc(15) + 0x280u);
+            x[18] = vs0(op, w3) + jc.c18;
+            x[19] = w3 + jc.c19;
+            x[20] = vs1(op, x[18]) + 0x80000000u;
+            x[21] = vs1(op, x[19]);
+            x[22] = vs1(op, x[20]) + 0x280u;
+            x[23] = vs1(op, x[21]) + jc.w16;
+            x[24] = vs1(op, x[22]) + jc.w17;
+            x[25] = vs1(op, x[23]) + x[18];
+            x[26] = vs1(op, x[24]) + x[19];
+            x[27] = vs1(op, x[25]) + x[20];
+            x[28] = vs1(op, x[26]) + x[21];
+            x[29] = vs1(op, x[27]) + x[22];
+            x[30] = vs1(op, x[28]) + x[23] + ssig0(0x280u);
+            x[31] = vs1(op, x[29]) + x[24] + jc.c31;
+            rnd(op, h, a, b, c, d, e, f, g, jc.kw16);
+            rnd(op, g, h, a, b, c, d, e, f, jc.kw17);
+            rnd(op, f, g, h, a, b, c, d, e, x[18], Kc(18));
+            rnd(op, e, f, g, h, a, b, c, d, x[19], Kc(19));
+            rnd(op, d, e, f, g, h, a, b, c, x[20], Kc(20));
+            rnd(op, c, d, e, f, g, h, a, b, x[21], Kc(21));
+            rnd(op, b, c, d, e, f, g, h, a, x[22], Kc(22));
+            rnd(op, a, b, c, d, e, f, g, h, x[23], Kc(23));
+            rnd(op, h, a, b, c, d, e, f, g, x[24], Kc(24));
+            rnd(op, g, h, a, b, c, d, e, f, x[25], Kc(25));
+            rnd(op, f, g, h, a, b, c, d, e, x[26], Kc(26));
+            rnd(op, e, f, g, h, a, b, c, d, x[27], Kc(27));
+            rnd(op, d, e, f, g, h, a, b, c, x[28], Kc(28));
+            rnd(op, c, d, e, f, g, h, a, b, x[29], Kc(29));
+            rnd(op, b, c, d, e, f, g, h, a, x[30], Kc(30));
+            rnd(op, a, b, c, d, e, f, g, h, x[31], Kc(31));
+            // roles after round 31 are (h,a,b,c,d,e,f,g): rename so (a..h) = (A..H)
+            {
+                const vw<V> t = h;
+                h = g; g = f; f = e; e = d; d = c; c = b; b = a; a = t;
+            }
+            w[0] = bc<V>(jc.w16); w[1] = bc<V>(jc.w17);
+#pragma unroll
+            for (int i = 18; i < 32; i++) w[i - 16] = x[i];
+        } else {
+            // ---------------- hash 2, rounds 0..31 ----------------
+            vw<V> x[32];
+            x[0] = a + jc.mid[0]; x[1] = b + jc.mid[1]; x[2] = c + jc.mid[2]; x[3] = d + jc.mid[3];
+            x[4] = e + jc.mid[4]; x[5] = f + jc.mid[5]; x[6] = g + jc.mid[6]; x[7] = h + jc.mid[7];
+            x[16] = vs0(op, x[1]) + x[0];
+            x[17] = vs0(op, x[2]) + x[1] + ssig1(0x100u);
+            x[18] = vs1(op, x[16]) + vs0(op, x[3]) + x[2];
+            x[19] = vs1(op, x[17]) + vs0(op, x[4]) + x[3];
+            x[20] = vs1(op, x[18]) + vs0(op, x[5]) + x[4];
+            x[21] = vs1(op, x[19]) + vs0(op, x[6]) + x[5];
+            x[22] = sched(op, x[20], bc<V>(0x100u), x[7], x[6]);
+            x[23] = vs1(op, x[21]) + x[16] + x[7] + ssig0(0x80000000u);
+            x[24] = vs1(op, x[22]) + x[17] + 0x80000000u;
+            x[25] = vs1(op, x[23]) + x[18];
+            x[26] = vs1(op, x[24]) + x[19];
+            x[27] = vs1(op, x[25]) + x[20];
+            x[28] = vs1(op, x[26]) + x[21];
+            x[29] = vs1(op, x[27]) + x[22];
+            x[30] = vs1(op, x[28]) + x[23] + ssig0(0x100u);
+            x[31] = vs1(op, x[29]) + x[24] + vs0(op, x[16]) + 0x100u;
+            a = bc<V>(IV0); b = bc<V>(IV1); c = bc<V>(IV2); d = bc<V>(IV3);
+            e = bc<V>(IV4); f = bc<V>(IV5); g = bc<V>(IV6); h = bc<V>(IV7);
+            {
+                const Ops<0> fold{};
+                rnd(fold, a, b, c, d, e, f, g, h, x[0], Kc(0));
+                rnd(fold, h, a, b, c, d, e, f, g, x[1], Kc(1));
+                rnd(fold, g, h, a, b, c, d, e, f, x[2], Kc(2));
+                rnd(fold, f, g, h, a, b, c, d, e, x[3], Kc(3));
+            }
+            rnd(op, e, f, g, h, a, b, c, d, x[4], Kc(4));
+            rnd(op, d, e, f, g, h, a, b, c, x[5], Kc(5));
+            rnd(op, c, d, e, f, g, h, a, b, x[6], Kc(6));
+            rnd(op, b, c, d, e, f, g, h, a, x[7], Kc(7));
+            rnd(op, a, b, c, d, e, f, g, h, Kc(8) + 0x80000000u);
+            rnd(op, h, a, b, c, d, e, f, g, Kc(9));
+            rnd(op, g, h, a, b, c, d, e, f, Kc(10));
+            rnd(op, f, g, h, a, b, c, d, e, Kc(11));
+            rnd(op, e, f, g, h, a, b, c, d, Kc(12));
+            rnd(op, d, e, f, g, h, a, b, c, Kc(13));
+            rnd(op, c, d, e, f, g, h, a, b, Kc(14));
+            rnd(op, b, c, d, e, f, g, h, a, Kc(15) + 0x100u);
+            rnd(op, a, b, c, d, e, f, g, h, x[16], Kc(16));
+            rnd(op, h, a, b, c, d, e, f, g, x[17], Kc(17));
+            rnd(op, g, h, a, b, c, d, e, f, x[18], Kc(18));
+            rnd(op, f, g, h, a, b, c, d, e, x[19], Kc(19));
+            rnd(op, e, f, g, h, a, b, c, d, x[20], Kc(20));
+            rnd(op, d, e, f, g, h, a, b, c, x[21], Kc(21));
+            rnd(op, c, d, e, f, g, h, a, b, x[22], Kc(22));
+            rnd(op, b, c, d, e, f, g, h, a, x[23], Kc(23));
+            rnd(op, a, b, c, d, e, f, g, h, x[24], Kc(24));
+            rnd(op, h, a, b, c, d, e, f, g, x[25], Kc(25));
+            rnd(op, g, h, a, b, c, d, e, f, x[26], Kc(26));
+            rnd(op, f, g, h, a, b, c, d, e, x[27], Kc(27));
+            rnd(op, e, f, g, h, a, b, c, d, x[28], Kc(28));
+            rnd(op, d, e, f, g, h, a, b, c, x[29], Kc(29));
+            rnd(op, c, d, e, f, g, h, a, b, x[30], Kc(30));
+            rnd(op, b, c, d, e, f, g, h, a, x[31], Kc(31));
+            // 32 rounds from the identity: (a..h) = (A..H) again
+#pragma unroll
+            for (int i = 16; i < 32; i++) w[i - 16] = x[i];
+        }
+        // ---------------- the shared generic blocks (rounds 32..47 [, 48..63]) ----------------
+        const int nblk = 2 - phase;
+#pragma unroll 1
+        for (int blk = 0; blk < nblk; blk++) generic16(op, w, a, b, c, d, e, f, g, h, 32 + 16 * blk);
+
+        if (phase == 1) {
+            // ---------------- hash 2 tail: rounds 48..60, e-chain only in 57..60 ----------------
+            OTD_GEN_W(0);  rnd(op, a, b, c, d, e, f, g, h, w[0], Kc(48));
+            OTD_GEN_W(1);  rnd(op, h, a, b, c, d, e, f, g, w[1], Kc(49));
+            OTD_GEN_W(2);  rnd(op, g, h, a, b, c, d, e, f, w[2], Kc(50));
+            OTD_GEN_W(3);  rnd(op, f, g, h, a, b, c, d, e, w[3], Kc(51));
+            OTD_GEN_W(4);  rnd(op, e, f, g, h, a, b, c, d, w[4], Kc(52));
+            OTD_GEN_W(5);  rnd(op, d, e, f, g, h, a, b, c, w[5], Kc(53));
+            OTD_GEN_W(6);  rnd(op, c, d, e, f, g, h, a, b, w[6], Kc(54));
+            OTD_GEN_W(7);  rnd(op, b, c, d, e, f, g, h, a, w[7], Kc(55));
+            OTD_GEN_W(8);  rnd(op, a, b, c, d, e, f, g, h, w[8], Kc(56));
+            OTD_GEN_W(9);  rnd_e(op, c, d, e, f, g, w[9], Kc(57));
+            OTD_GEN_W(10); rnd_e(op, b, c, d, e, f, w[10], Kc(58));
+            OTD_GEN_W(11); rnd_e(op, a, b, c, d, e, w[11], Kc(59));
+            OTD_GEN_W(12); rnd_e(op, h, a, b, c, d, w[12], Kc(60));
+            result = h;
+        }
+    }
+    return result;
+}
+#undef OTD_GEN_W
 
 // e after round 60 for which digest word 7 is zero.
 constexpr uint32_t kE60ForZeroTop = 0u - IV7;

@@ -67,8 +67,9 @@ __device__ __forceinline__ void ring_push_warp(bool hit, uint32_t nonce, uint32_
 
 // V: candidates interleaved per thread; ITER: sequential batches per thread;
 // KN: instruction-placement knobs (scan_core.cuh).
-template <int V, int ITER, unsigned KN>
-__global__ void __launch_bounds__(kScanBlock)
+// MINB: minimum resident blocks per SM handed to __launch_bounds__ (register budget = 65536 / (256*MINB)).
+template <int V, int ITER, unsigned KN, bool HALF = false, int MINB = 1>
+__global__ void __launch_bounds__(kScanBlock, MINB)
 scan_kernel(const __grid_constant__ JobConsts jc, const __grid_constant__ PipeMults pm,
             uint32_t nonce_begin, unsigned long long count,
             uint32_t instance, RingHeader* ring, RingEntry* entries, uint32_t cap,
@@ -88,7 +89,7 @@ scan_kernel(const __grid_constant__ JobConsts jc, const __grid_constant__ PipeMu
 #pragma unroll
         for (int v = 0; v < V; v++)
             w3.x[v] = __byte_perm(nonce_begin + (uint32_t)idx0 + (uint32_t)(v * kScanBlock), 0, 0x0123);
-        const vw<V> e60 = scan_core<V, KN>(jc, w3, op);
+        const vw<V> e60 = (KN & KN_COMPACT) ? scan_core_compact<V, KN>(jc, w3, op) : scan_core<V, KN, HALF>(jc, w3, op);
 
         unsigned cmask = 0;
 #pragma unroll

@@ -13,21 +13,26 @@ struct RingHeader;
 struct RingEntry;
 }  // namespace otd
 
-// index, name, V, ITER, knobs
-#define OTD_KN_FREE (otd::KN_E | otd::KN_W1 | otd::KN_SSHR)
+// index, name, V, ITER, knobs, HALF, MINB.  Production variants first (indices below
+// OTD_NUM_PRODUCTION_VARIANTS); the rest are performance experiments: "h_*" variants
+// stop after hash 1 (HALF) and do NOT compute SHA-256d — the library refuses to run
+// them unless the environment says OTD_ALLOW_EXPERIMENTAL=1.
+//
+// Measured on B200 (profiles/r1_variant_sweep.log), GH/s per GPU over a full 2^32 scan:
+//   add_t1x_b5 9.25 | add_t1x_b4 9.25 | c_add_t1x_b4 9.00 | alu_b5 8.25 | c_alu_b4 8.16
+#define OTD_KN_ADD1 (otd::KN_E | otd::KN_W1)               /* 2-input adds: one IMAD replaces one ALU add */
+#define OTD_KN_ADDS (OTD_KN_ADD1 | otd::KN_A | otd::KN_W2) /* every immediate-free add except t1's */
+#define OTD_KN_BEST (OTD_KN_ADDS | otd::KN_T1X)            /* ... plus t1 split without an immediate IMAD */
 #define OTD_SCAN_VARIANTS(X)                                                                        \
-    X(0, "alu", 1, 16, 0u)                                                                          \
-    X(1, "free", 1, 16, OTD_KN_FREE)                                                                \
-    X(2, "hkw_bs1", 1, 16, OTD_KN_FREE | otd::KN_HKW | otd::KN_BS1)                                 \
-    X(3, "bal", 1, 16, OTD_KN_FREE | otd::KN_HKW | otd::KN_BS1 | otd::KN_BS0 | otd::KN_SROT)        \
-    X(4, "bal_nosrot", 1, 16, OTD_KN_FREE | otd::KN_HKW | otd::KN_BS1 | otd::KN_BS0)                \
-    X(5, "bal_nobs0", 1, 16, OTD_KN_FREE | otd::KN_HKW | otd::KN_BS1 | otd::KN_SROT)                \
-    X(6, "bal_nohkw", 1, 16, OTD_KN_FREE | otd::KN_BS1 | otd::KN_BS0 | otd::KN_SROT)                \
-    X(7, "bal_w2", 1, 16, OTD_KN_FREE | otd::KN_HKW | otd::KN_BS1 | otd::KN_BS0 | otd::KN_SROT | otd::KN_W2) \
-    X(8, "allfma", 1, 16, 1023u)                                                                    \
-    X(9, "bal_v2", 2, 8, OTD_KN_FREE | otd::KN_HKW | otd::KN_BS1 | otd::KN_BS0 | otd::KN_SROT)      \
-    X(10, "alu_v2", 2, 8, 0u)
+    X(0, "add_t1x_b5", 1, 16, OTD_KN_BEST, false, 5)                                                \
+    X(1, "alu_b5", 1, 16, 0u, false, 5)                                                             \
+    X(2, "c_add_t1x_b4", 1, 16, otd::KN_COMPACT | OTD_KN_BEST, false, 4)                            \
+    X(3, "c_alu_b4", 1, 16, otd::KN_COMPACT, false, 4)                                              \
+    X(4, "add_t1x_v2_b2", 2, 8, OTD_KN_BEST, false, 2)                                              \
+    X(5, "h_alu", 1, 16, 0u, true, 5)                                                               \
+    X(6, "h_add_t1x", 1, 16, OTD_KN_BEST, true, 5)
 
+#define OTD_NUM_PRODUCTION_VARIANTS 5
 #define OTD_DEFAULT_VARIANT 0
 
 typedef cudaError_t (*otd_scan_launch_fn)(const otd::JobConsts&, uint32_t nonce_begin,
@@ -35,7 +40,7 @@ typedef cudaError_t (*otd_scan_launch_fn)(const otd::JobConsts&, uint32_t nonce_
                                           otd::RingHeader*, otd::RingEntry*, uint32_t cap,
                                           const unsigned int* stop, unsigned int gen, cudaStream_t);
 
-#define OTD_DECLARE_VARIANT(idx, name, v, iter, kn)                                                   \
+#define OTD_DECLARE_VARIANT(idx, name, v, iter, kn, half, minb)                                                   \
     cudaError_t otd_scan_launch_##idx(const otd::JobConsts&, uint32_t, unsigned long long, uint32_t, \
                                       otd::RingHeader*, otd::RingEntry*, uint32_t, const unsigned int*, \
                                       unsigned int, cudaStream_t);

@@ -57,7 +57,7 @@ OTD_HD constexpr uint32_t bswap32(uint32_t x)
 
 // Runtime-indexed K table for the looped (non-unrolled) compression.
 #if defined(__CUDACC__)
-__device__ __constant__ const uint32_t kKdev[64] = {OTD_K_LIST};
+__device__ __constant__ __align__(16) const uint32_t kKdev[64] = {OTD_K_LIST};
 #endif
 static const uint32_t kKhost[64] = {OTD_K_LIST};
 

@@ -11,7 +11,7 @@ static void run_core(const JobConsts& jc, const uint32_t* nonces, uint32_t* out)
     vw<V> w3;
     for (int i = 0; i < V; i++) w3.x[i] = bswap32(nonces[i]);
     const Ops<KN> op{make_pipe_mults()};
-    vw<V> r = scan_core<V, KN>(jc, w3, op);
+    vw<V> r = (KN & KN_COMPACT) ? scan_core_compact<V, KN>(jc, w3, op) : scan_core<V, KN>(jc, w3, op);
     for (int i = 0; i < V; i++) out[i] = r.x[i];
 }
 template <unsigned KN>
@@ -54,6 +54,20 @@ int fc_scan_e60_kn(const uint8_t hdr76[76], const uint32_t* nonces, int v, unsig
         case KN_E | KN_W1 | KN_SSHR | KN_HKW | KN_BS1 | KN_BS0 | KN_SROT:
             return run_v<KN_E | KN_W1 | KN_SSHR | KN_HKW | KN_BS1 | KN_BS0 | KN_SROT>(jc, nonces, v, e60_out);
         case KN_T1 | KN_A | KN_W2: return run_v<KN_T1 | KN_A | KN_W2>(jc, nonces, v, e60_out);
+        case 63: return run_v<63>(jc, nonces, v, e60_out);
+        case KN_E | KN_W1 | KN_A: return run_v<KN_E | KN_W1 | KN_A>(jc, nonces, v, e60_out);
+        case KN_E | KN_W1 | KN_A | KN_T1X: return run_v<KN_E | KN_W1 | KN_A | KN_T1X>(jc, nonces, v, e60_out);
+        case KN_E | KN_W1 | KN_A | KN_T1X | KN_W2: return run_v<KN_E | KN_W1 | KN_A | KN_T1X | KN_W2>(jc, nonces, v, e60_out);
+        case KN_E | KN_W1 | KN_T1X: return run_v<KN_E | KN_W1 | KN_T1X>(jc, nonces, v, e60_out);
+        case KN_E | KN_W1 | KN_A | KN_W2: return run_v<KN_E | KN_W1 | KN_A | KN_W2>(jc, nonces, v, e60_out);
+        case 2047: return run_v<2047>(jc, nonces, v, e60_out);
+        case KN_COMPACT: return run_v<KN_COMPACT>(jc, nonces, v, e60_out);
+        case KN_COMPACT | KN_E | KN_W1 | KN_A | KN_W2 | KN_T1X: return run_v<KN_COMPACT | KN_E | KN_W1 | KN_A | KN_W2 | KN_T1X>(jc, nonces, v, e60_out);
+        case KN_COMPACT | KN_E | KN_W1 | KN_A | KN_W2 | KN_T1: return run_v<KN_COMPACT | KN_E | KN_W1 | KN_A | KN_W2 | KN_T1>(jc, nonces, v, e60_out);
+        case KN_COMPACT | KN_E | KN_W1 | KN_A | KN_W2: return run_v<KN_COMPACT | KN_E | KN_W1 | KN_A | KN_W2>(jc, nonces, v, e60_out);
+        case KN_COMPACT | KN_E | KN_W1 | KN_A: return run_v<KN_COMPACT | KN_E | KN_W1 | KN_A>(jc, nonces, v, e60_out);
+        case KN_E | KN_W1 | KN_A | KN_W2 | KN_T1: return run_v<KN_E | KN_W1 | KN_A | KN_W2 | KN_T1>(jc, nonces, v, e60_out);
+        case KN_COMPACT | 1023u | KN_T1X: return run_v<KN_COMPACT | 1023u | KN_T1X>(jc, nonces, v, e60_out);
         default: return -2;
     }
 }
