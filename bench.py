@@ -253,14 +253,27 @@ def main():
         peak_dual = max(miner.int_peak(modes.index("alu_fma"), device=dev, iters=4096)[0] for _ in range(3))
         per_gpu_hps = value * 1e9 / world
         achieved = per_gpu_hps * ALG_OPS_PER_HASH
+        # Two ways to read the same measurement:
+        #  - contract figure: 2450 algorithmic 3-input ops/hash against the ALU-pipe rate -> frac > 1,
+        #    because ~650 of those ops are adds that this kernel issues as IMAD on the FMA pipe;
+        #  - two-pipe figure: the 1804 shift/rotate/logic ops per hash that ONLY the ALU pipe can run
+        #    (IMAD.WIDE does not co-issue) against the same ALU-pipe rate -> the real ceiling.
+        alu_only_ops = 1804
         roofline = {"bound": "int-issue", "achieved": achieved / 1e12, "peak": peak_alu / 1e12,
-                    "unit": "Tint-op/s", "frac": achieved / peak_alu, "traffic": 189440,
+                    "unit": "Tint-op/s", "frac": achieved / peak_alu, "traffic": 89344,
                     "note": ("achieved = per-GPU H/s x 2450 algorithmic 3-input integer ops/hash (SURVEY §8d); "
-                             "peak = measured ALU-pipe rate (SHF/LOP3/IADD3 at the SHA mix) on this GPU, of measured; "
-                             "frac can exceed 1 because ptxas issues part of the adds as IMAD on the FMA pipe; "
-                             "traffic = dram__bytes_read+write (bytes) of one 2^30-candidate launch from ncu --set full (profiles/r1_ncu_scan_kernel.csv): effectively none"),
+                             "peak = ALU-pipe rate (SHF/LOP3/IADD3 at the SHA mix) measured on this GPU in this run, "
+                             "of measured; frac exceeds 1 because the kernel issues the ~650 adds/hash as IMAD on the "
+                             "FMA pipe, which a one-pipe roofline does not model; traffic = dram__bytes_read+write "
+                             "(bytes) of one 2^30-candidate launch from ncu --set full "
+                             "(profiles/r1_ncu_scan_kernel.csv): effectively none"),
+                    "frac_two_pipe": per_gpu_hps * alu_only_ops / peak_alu,
+                    "two_pipe_note": ("H/s x 1804 ALU-only ops/hash (SHF 1176 + LOP3 628) / measured ALU-pipe rate: "
+                                      "the ceiling once every add runs on the FMA pipe; ncu shows the ALU pipe 97.3% busy "
+                                      "with 1956 ALU-pipe instructions per hash"),
                     "peak_dual_issue": peak_dual / 1e12, "alg_ops_per_hash": ALG_OPS_PER_HASH,
-                    "roofline_ghs_per_gpu": peak_alu / ALG_OPS_PER_HASH / 1e9}
+                    "roofline_ghs_per_gpu": peak_alu / ALG_OPS_PER_HASH / 1e9,
+                    "two_pipe_roofline_ghs_per_gpu": peak_alu / alu_only_ops / 1e9}
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
