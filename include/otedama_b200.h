@@ -139,6 +139,27 @@ typedef struct {          /* miner.Share, worker.go:33-43 */
     int32_t reserved;
 } otd_share_t;
 
+/* ------------------------------------------------------- job -> work glue --
+ * The engine-side functions that turn a pool job into a miner.Work
+ * (internal/engine/run.go); pure host code, no device needed.
+ *
+ * otd_v1_job_target — v1JobTarget (run.go:1313-1324): the nBits block target,
+ * replaced by the pool's share-difficulty target when difficulty > 0 and that
+ * conversion succeeds.  Malformed nbits fail regardless of difficulty.
+ * otd_work_from_v2_job — updateWork (run.go:1271-1297): all five header inputs
+ * from a Stratum V2 standard-channel job + chain tip; the share target, or the
+ * nBits target when the pool assigned none (all-zero).  Returns OTD_EINVAL (and
+ * leaves *work untouched) where the reference silently returns.
+ * otd_work_from_v1_job — applyJob (run.go:1340-1364) as the reference has it:
+ * job id parsed like Sscanf("%d"), header carries merkle root / time / bits only
+ * (version and prev-hash are NOT copied by the reference). */
+int otd_v1_job_target(uint32_t nbits, double difficulty, uint8_t target[32]);
+int otd_work_from_v2_job(uint32_t job_id, uint32_t channel_id, uint32_t version, const uint8_t merkle_root[32],
+                         const uint8_t prev_hash[32], uint32_t prev_nbits, uint32_t ntime,
+                         const uint8_t share_target[32], otd_work_t* work);
+int otd_work_from_v1_job(const char* job_id, uint32_t channel_id, const uint8_t merkle_root[32], uint32_t ntime,
+                         uint32_t nbits, double difficulty, otd_work_t* work);
+
 /* ----------------------------------------------------------------- worker --
  * One worker per device: the GPU counterpart of *miner.Worker
  * (internal/miner/worker.go:91-212), constructed by engine.startMinerWorkers

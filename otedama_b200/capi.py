@@ -85,6 +85,10 @@ _SIGS = {
     "otd_target_from_difficulty": (c_int, [c_double, c_char_p]),
     "otd_meets_target": (c_int, [c_char_p, c_uint32]),
     "otd_hash_headers": (c_int, [c_int, c_char_p, c_size_t, c_char_p]),
+    "otd_v1_job_target": (c_int, [c_uint32, c_double, c_char_p]),
+    "otd_work_from_v2_job": (c_int, [c_uint32, c_uint32, c_uint32, c_char_p, c_char_p, c_uint32, c_uint32, c_char_p,
+                                     POINTER(CWork)]),
+    "otd_work_from_v1_job": (c_int, [c_char_p, c_uint32, c_char_p, c_uint32, c_uint32, c_double, POINTER(CWork)]),
     "otd_worker_create": (c_void_p, [c_int, POINTER(CWorkerConfig)]),
     "otd_worker_set_work": (c_int64, [c_void_p, POINTER(CWork)]),
     "otd_worker_poll_shares": (c_int, [c_void_p, POINTER(CShare), c_int, c_int]),

@@ -299,6 +299,80 @@ extern "C" int otd_meets_target(const uint8_t hash[32], uint32_t nbits)
     return otd_hash_less_or_equal(hash, t);
 }
 
+// --------------------------------------------------------- job -> work glue --
+extern "C" int otd_v1_job_target(uint32_t nbits, double difficulty, uint8_t target[32])
+{
+    int rc = otd_target_from_nbits(nbits, target);
+    if (rc) return rc;
+    if (difficulty > 0) {
+        uint8_t dt[32];
+        if (otd_target_from_difficulty(difficulty, dt) == OTD_OK) memcpy(target, dt, 32);
+    }
+    return OTD_OK;
+}
+
+extern "C" int otd_work_from_v2_job(uint32_t job_id, uint32_t channel_id, uint32_t version,
+                                    const uint8_t merkle_root[32], const uint8_t prev_hash[32], uint32_t prev_nbits,
+                                    uint32_t ntime, const uint8_t share_target[32], otd_work_t* work)
+{
+    if (!merkle_root || !prev_hash || !share_target || !work) return fail(OTD_EINVAL, "otd_work_from_v2_job: NULL argument");
+    uint8_t target[32];
+    memcpy(target, share_target, 32);
+    bool zero = true;
+    for (int i = 0; i < 32; i++) zero = zero && target[i] == 0;
+    if (zero) {
+        int rc = otd_target_from_nbits(prev_nbits, target);
+        if (rc) return rc;
+    }
+    otd_work_t w;
+    memset(&w, 0, sizeof w);
+    w.job_id = job_id;
+    w.channel_id = channel_id;
+    w.header.version = version;
+    memcpy(w.header.prev_hash, prev_hash, 32);
+    memcpy(w.header.merkle_root, merkle_root, 32);
+    w.header.time = ntime;
+    w.header.bits = prev_nbits;
+    w.nbits = prev_nbits;
+    memcpy(w.target, target, 32);
+    *work = w;
+    return OTD_OK;
+}
+
+extern "C" int otd_work_from_v1_job(const char* job_id, uint32_t channel_id, const uint8_t merkle_root[32],
+                                    uint32_t ntime, uint32_t nbits, double difficulty, otd_work_t* work)
+{
+    if (!job_id || !merkle_root || !work) return fail(OTD_EINVAL, "otd_work_from_v1_job: NULL argument");
+    uint8_t target[32];
+    int rc = otd_v1_job_target(nbits, difficulty, target);
+    if (rc) return fail(rc, std::string("engine: bad target for job \"") + job_id + "\": " + otd_last_error());
+    // fmt.Sscanf(job.JobID, "%d", &jobID) with a uint32 destination: optional sign, decimal digits,
+    // leading spaces skipped, trailing text ignored, value must fit
+    const char* p = job_id;
+    while (*p == ' ' || *p == '\t') p++;
+    bool neg = false;
+    if (*p == '+' || *p == '-') { neg = *p == '-'; p++; }
+    if (*p < '0' || *p > '9' || neg)
+        return fail(OTD_EINVAL, std::string("engine: unparseable job ID \"") + job_id + "\"");
+    unsigned long long v = 0;
+    while (*p >= '0' && *p <= '9') {
+        v = v * 10 + (unsigned)(*p - '0');
+        if (v > 0xffffffffull) return fail(OTD_EINVAL, std::string("engine: unparseable job ID \"") + job_id + "\"");
+        p++;
+    }
+    otd_work_t w;
+    memset(&w, 0, sizeof w);
+    w.job_id = (uint32_t)v;
+    w.channel_id = channel_id;
+    memcpy(w.header.merkle_root, merkle_root, 32);
+    w.header.time = ntime;
+    w.header.bits = nbits;
+    w.nbits = nbits;
+    memcpy(w.target, target, 32);
+    *work = w;
+    return OTD_OK;
+}
+
 // ------------------------------------------------------------ scan variants --
 struct ScanVariant {
     const char* name;

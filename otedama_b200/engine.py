@@ -1,0 +1,89 @@
+"""Host-side mirror of the engine functions that feed the hot path
+(internal/engine/run.go:1271-1364): job -> miner.Work -> Worker.SetWork.  The
+work-building logic lives behind the C ABI (otd_work_from_v2_job /
+otd_work_from_v1_job / otd_v1_job_target) so the Go shim binds the same code."""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Iterable
+
+from . import capi, miner
+from .capi import CWork, lib
+
+
+class EngineError(ValueError):
+    """The Go functions' non-nil ``error`` return."""
+
+
+@dataclass
+class NewMiningJob:
+    """stratum.NewMiningJob (internal/stratum/messages.go:89-96)."""
+    channel_id: int = 0
+    job_id: int = 0
+    has_min_ntime: bool = False
+    min_ntime: int = 0
+    version: int = 0
+    merkle_root: bytes = b"\x00" * 32
+
+
+@dataclass
+class Job:
+    """poolproto.Job as applyJob uses it (internal/poolproto/poolproto.go:140-169)."""
+    job_id: str = ""
+    ntime: int = 0
+    nbits: int = 0
+    version: int = 0
+    prev_hash: bytes = b"\x00" * 32
+    merkle_root: bytes = b"\x00" * 32
+    clean_jobs: bool = False
+
+
+def _work_from_c(cw: CWork) -> miner.Work:
+    h = cw.header
+    return miner.Work(job_id=cw.job_id, channel_id=cw.channel_id, nbits=cw.nbits, target=bytes(cw.target),
+                      header=miner.Header(h.version, bytes(h.prev_hash), bytes(h.merkle_root), h.time, h.bits, 0))
+
+
+def v1_job_target(nbits: int, difficulty: float) -> bytes:
+    """v1JobTarget (run.go:1313-1324)."""
+    out = ctypes.create_string_buffer(32)
+    if lib().otd_v1_job_target(nbits & 0xFFFFFFFF, float(difficulty), out) < 0:
+        raise EngineError(capi.last_error())
+    return out.raw
+
+
+def work_from_v2_job(job: NewMiningJob, chan_id: int, prev_hash: bytes, prev_nbits: int, ntime: int,
+                     share_target: bytes):
+    """The Work updateWork builds, or None where the reference silently returns."""
+    cw = CWork()
+    rc = lib().otd_work_from_v2_job(job.job_id, chan_id, job.version & 0xFFFFFFFF, bytes(job.merkle_root),
+                                    bytes(prev_hash), prev_nbits & 0xFFFFFFFF, ntime & 0xFFFFFFFF,
+                                    bytes(share_target), ctypes.byref(cw))
+    return _work_from_c(cw) if rc == 0 else None
+
+
+def update_work(workers: Iterable, job: NewMiningJob, chan_id: int, prev_hash: bytes, prev_nbits: int, ntime: int,
+                share_target: bytes) -> None:
+    """updateWork (run.go:1271-1297): point every worker at the job."""
+    w = work_from_v2_job(job, chan_id, prev_hash, prev_nbits, ntime, share_target)
+    if w is None:
+        return
+    for wr in workers:
+        wr.set_work(w)
+
+
+def work_from_v1_job(job: Job, chan_id: int, difficulty: float) -> miner.Work:
+    cw = CWork()
+    rc = lib().otd_work_from_v1_job(job.job_id.encode(), chan_id, bytes(job.merkle_root), job.ntime & 0xFFFFFFFF,
+                                    job.nbits & 0xFFFFFFFF, float(difficulty), ctypes.byref(cw))
+    if rc < 0:
+        raise EngineError(capi.last_error())
+    return _work_from_c(cw)
+
+
+def apply_job(workers: Iterable, job: Job, chan_id: int, difficulty: float) -> None:
+    """applyJob (run.go:1340-1364); raises where the reference returns an error."""
+    w = work_from_v1_job(job, chan_id, difficulty)
+    for wr in workers:
+        wr.set_work(w)

@@ -361,7 +361,7 @@ def hash_rate_string(hps: float) -> str:
     for lim, unit in ((1e12, "TH/s"), (1e9, "GH/s"), (1e6, "MH/s"), (1e3, "kH/s")):
         if hps >= lim:
             return f"{hps / lim:.2f} {unit}"
-    return f"{hps:.2f} H/s"
+    return f"{hps:.0f} H/s"
 
 
 # ----------------------------------------------------------------------------

@@ -163,3 +163,11 @@ def test_hal_identity_rules(product):
             hal.Identity(bad, "gpu", "nvidia", "x").validate()
     assert hal.CudaDriver().name() == "cuda"
     assert isinstance(hal.CudaDriver().enumerate(), list)
+
+
+def test_hash_rate_string(product):
+    """TestHashRateString (internal/miner/worker_test.go:246-265), same vectors."""
+    from otedama_b200 import miner
+    for hps, want in ((500, "500 H/s"), (1500, "1.50 kH/s"), (2.5e6, "2.50 MH/s"), (3.7e9, "3.70 GH/s"),
+                      (120e12, "120.00 TH/s")):
+        assert miner.hash_rate_string(hps) == want

@@ -409,6 +409,56 @@ def test_worker_full_range_at_difficulty_one(miner):
         assert st.hashes_total == 1 << 32 and st.hash_rate > 1e9
 
 
+def test_worker_runs_rolled_work_like_the_synchronous_scan(miner, oracle):
+    """extranonce2 x version x nonce through the asynchronous worker path (K3 -> K2 -> K1
+    with two launches in flight) gives exactly the synchronous scan's share set."""
+    c3 = W.config3_v1()
+    t = oracle.target_from_difficulty(2.0 ** -20)
+    work, f = v1_work(miner, c3, job_id=77, target=t, extranonce2_begin=2, extranonce2_count=9, extranonce2_stride=4,
+                      version_mask=W.BIP320_MASK, version_begin=1, version_count=5, version_stride=3,
+                      nonce_begin=0x80000000, nonce_count=1 << 14)
+    want = miner.scan(work)
+    with miner.Worker(miner.WorkerConfig(launch_log2=16)) as w:
+        w.set_work(work)
+        assert w.wait_exhausted(20000)
+        got = []
+        while True:
+            part = w.poll_shares(4096, 0)
+            if not part:
+                break
+            got += part
+        st = w.stats()
+    assert key(got) == key(want.shares) and len(got) > 30
+    assert st.hashes_total == want.hashes == 45 << 14 and st.launches == 45
+    assert all(s.job_id == 77 for s in got)
+    # and a few of them against the oracle, end to end
+    for s in got[:5]:
+        root = oracle.v1_merkle_root(c3["coinb1"], c3["extranonce1"], oracle.extranonce2_bytes(s.extranonce2, 8),
+                                     c3["coinb2"], c3["branches"])
+        oh = oracle.Header(s.version, c3["prev_hash"], root, s.ntime, c3["bits"], s.nonce)
+        assert oracle.hash_header(oh) == s.hash and oracle.less_or_equal(s.hash, t)
+
+
+def test_two_workers_on_one_device_do_not_disturb_each_other(miner, oracle):
+    t = oracle.target_from_difficulty(2.0 ** -18)
+    jobs = []
+    for i in (21, 22):
+        f = W.config2_fields(i)
+        jobs.append(miner.Work(job_id=i, header=mheader(miner, f), target=t, nonce_count=1 << 22))
+    want = [miner.scan(j) for j in jobs]
+    ws = [miner.Worker(miner.WorkerConfig(launch_log2=18)).start() for _ in jobs]
+    try:
+        for w, j in zip(ws, jobs):
+            w.set_work(j)
+        for w, j, r in zip(ws, jobs, want):
+            assert w.wait_exhausted(20000)
+            got = w.poll_shares(4096, 0)
+            assert key(got) == key(r.shares) and all(s.job_id == j.job_id for s in got) and len(got) > 5
+    finally:
+        for w in ws:
+            w.stop()
+
+
 def test_two_workers_partition_the_version_space(miner, oracle):
     """static partition, no communication — version index k -> k mod G.
     Runs both halves on device 0 when only one GPU is visible."""
