@@ -98,6 +98,21 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------- CPU arms --
+def cpu_extra_numbers():
+    """Single-thread and midstate ("strong") CPU numbers, informational, ~2 s each."""
+    from oracle import oracle as o
+    from tests import workloads as wl
+    h = wl.genesis_header()
+    target = o.target_from_nbits(0x1D00FFFF)
+    out = {}
+    for name, threads, mid, count in (("single_thread_mhs", 1, False, 1 << 22),
+                                      ("midstate_all_threads_mhs", os.cpu_count() or 1, True, 1 << 26)):
+        t0 = time.time()
+        _, _, n = o.grind(h, target, 0, count, threads=threads, midstate=mid)
+        out[name] = n / (time.time() - t0) / 1e6
+    return out
+
+
 def cpu_grind_sample(seconds_target: float, threads: int):
     """The oracle's restatement of Worker.grind (reference arithmetic: serialise +
     3 compressions per nonce) on a bounded nonce window of the genesis header."""
@@ -278,7 +293,8 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             rate, n, dt, backend = cpu_grind_sample(args.cpu_seconds, threads)
-            cpu = {"value": rate / 1e6, "unit": "MH/s", "cores": threads, "kind": "port",
+            extra = cpu_extra_numbers()
+            cpu = {"value": rate / 1e6, "unit": "MH/s", "cores": threads, "kind": "port", **extra,
                    "sample": f"{n} nonces of the genesis header around nonce 2083236893 in {dt:.1f}s, 3 compressions "
                              f"per nonce like Worker.grind (no midstate), {backend} compression, {cpu_model()}"}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

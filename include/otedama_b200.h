@@ -59,6 +59,18 @@ typedef struct {
 int otd_device_count(void);                               /* >= 0, or OTD_E* */
 int otd_device_info(int device_index, otd_device_info_t* out);
 
+/* Live device telemetry for the engine's efficiency gauges
+ * (otedama_joules_per_terahash, internal/engine/metrics.go:488; per-device sampling
+ * in internal/engine/stats.go:123-137): board power, SM clock, temperature, read
+ * through NVML (loaded at run time; OTD_ENODEV if the driver library is absent).
+ * joules per terahash = power_w / (hash_rate / 1e12). */
+typedef struct {
+    double power_w;
+    double sm_clock_mhz;
+    double temperature_c;
+} otd_telemetry_t;
+int otd_device_telemetry(int device_index, otd_telemetry_t* out);
+
 /* ------------------------------------------------------------ header math --
  * Host-side mirrors of internal/miner/sha256d.go helpers (once per job). */
 typedef struct {            /* miner.Header, sha256d.go:49-56 */

@@ -85,7 +85,7 @@ def build(force: bool = False, verbose: bool = False, jobs: int = 0) -> str:
         if p not in keep:
             os.remove(p)
     nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH] + [t[1] for t in tasks]
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH] + [t[1] for t in tasks] + ["-ldl"]
     proc = subprocess.run(cmd, capture_output=True, text=True)
     log.append(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
     with open(os.path.join(_PKG, "build.log"), "w") as fh:

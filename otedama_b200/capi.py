@@ -34,6 +34,10 @@ class DeviceInfo(Structure):
                 ("cap_sha256d", c_int32), ("cap_general_compute", c_int32)]
 
 
+class CTelemetry(Structure):
+    _fields_ = [("power_w", c_double), ("sm_clock_mhz", c_double), ("temperature_c", c_double)]
+
+
 class CHeader(Structure):
     _fields_ = [("version", c_uint32), ("prev_hash", c_uint8 * 32), ("merkle_root", c_uint8 * 32),
                 ("time", c_uint32), ("bits", c_uint32), ("nonce", c_uint32)]
@@ -77,6 +81,7 @@ _SIGS = {
     "otd_abi_version": (c_int, []),
     "otd_device_count": (c_int, []),
     "otd_device_info": (c_int, [c_int, POINTER(DeviceInfo)]),
+    "otd_device_telemetry": (c_int, [c_int, POINTER(CTelemetry)]),
     "otd_header_bytes": (None, [POINTER(CHeader), c_char_p]),
     "otd_parse_header": (None, [c_char_p, POINTER(CHeader)]),
     "otd_hash_less_or_equal": (c_int, [c_char_p, c_char_p]),

@@ -8,6 +8,7 @@
 // CPU hashing path in this library: candidates are hashed, confirmed and turned
 // into 32-byte hashes on the device.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <algorithm>
 #include <atomic>
@@ -95,6 +96,54 @@ extern "C" int otd_device_info(int idx, otd_device_info_t* out)
     // the kernels are built for sm_100a only
     out->cap_sha256d = (p.major == 10) ? 1 : 0;
     out->cap_general_compute = 1;
+    return OTD_OK;
+}
+
+// --------------------------------------------------------------- telemetry --
+// NVML is bound at run time so the library has no link-time dependency on it.
+namespace {
+struct Nvml {
+    void* lib = nullptr;
+    int (*init)() = nullptr;
+    int (*by_bus)(const char*, void**) = nullptr;
+    int (*power)(void*, unsigned int*) = nullptr;
+    int (*clock)(void*, int, unsigned int*) = nullptr;
+    int (*temp)(void*, int, unsigned int*) = nullptr;
+    bool ok = false;
+};
+Nvml& nvml()
+{
+    static Nvml n = [] {
+        Nvml m;
+        m.lib = dlopen("libnvidia-ml.so.1", RTLD_NOW | RTLD_LOCAL);
+        if (!m.lib) return m;
+        m.init = (int (*)())dlsym(m.lib, "nvmlInit_v2");
+        m.by_bus = (int (*)(const char*, void**))dlsym(m.lib, "nvmlDeviceGetHandleByPciBusId_v2");
+        m.power = (int (*)(void*, unsigned int*))dlsym(m.lib, "nvmlDeviceGetPowerUsage");
+        m.clock = (int (*)(void*, int, unsigned int*))dlsym(m.lib, "nvmlDeviceGetClockInfo");
+        m.temp = (int (*)(void*, int, unsigned int*))dlsym(m.lib, "nvmlDeviceGetTemperature");
+        m.ok = m.init && m.by_bus && m.power && m.clock && m.temp && m.init() == 0;
+        return m;
+    }();
+    return n;
+}
+}  // namespace
+
+extern "C" int otd_device_telemetry(int device_index, otd_telemetry_t* out)
+{
+    if (!out) return fail(OTD_EINVAL, "otd_device_telemetry: out is NULL");
+    int rc = check_device(device_index);
+    if (rc) return rc;
+    Nvml& n = nvml();
+    if (!n.ok) return fail(OTD_ENODEV, "NVML (libnvidia-ml.so.1) is not available");
+    char bus[32] = {0};
+    CU_TRY(cudaDeviceGetPCIBusId(bus, sizeof bus, device_index));
+    void* h = nullptr;
+    if (n.by_bus(bus, &h) != 0 || !h) return fail(OTD_ENODEV, std::string("NVML has no device at ") + bus);
+    unsigned int mw = 0, mhz = 0, t = 0;
+    out->power_w = n.power(h, &mw) == 0 ? mw / 1000.0 : -1.0;
+    out->sm_clock_mhz = n.clock(h, 1 /* NVML_CLOCK_SM */, &mhz) == 0 ? (double)mhz : -1.0;
+    out->temperature_c = n.temp(h, 0 /* NVML_TEMPERATURE_GPU */, &t) == 0 ? (double)t : -1.0;
     return OTD_OK;
 }
 

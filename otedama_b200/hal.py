@@ -53,6 +53,13 @@ class CudaDevice:
     def capabilities(self) -> Capabilities:
         return Capabilities(bool(self.info.cap_sha256d), bool(self.info.cap_general_compute))
 
+    def telemetry(self):
+        """(power_w, sm_clock_mhz, temperature_c) via NVML — feeds joules-per-terahash."""
+        from .capi import CTelemetry
+        t = CTelemetry()
+        check(lib().otd_device_telemetry(self.index, ctypes.byref(t)))
+        return t.power_w, t.sm_clock_mhz, t.temperature_c
+
     def shutdown(self) -> None:
         """Idempotent, like the reference requires (device.go:165-169)."""
         self._shutdown = True

@@ -51,6 +51,25 @@ def full_genesis():
     print("genesis_full_scan.json:", doc["shares"], f"{hashes / dt / 1e6:.1f} MH/s")
 
 
+def full_synthetic(index=1):
+    """Full 2^32 CPU scan of one synthetic configs[1] header at difficulty 1 (midstate path —
+    cross-checked against the 3-compression path by tests/test_oracle.py on windows)."""
+    h = wl.config2_header(index)
+    target = o.target_from_difficulty(1.0)
+    threads = os.cpu_count() or 1
+    t0 = time.time()
+    shares, dropped, hashes = o.grind(h, target, 0, 1 << 32, threads=threads, midstate=True)
+    dt = time.time() - t0
+    assert dropped == 0 and hashes == 1 << 32
+    doc = {"what": f"full 2^32 nonce scan of synthetic configs[1] header {index} at difficulty 1 on the CPU oracle",
+           "index": index, "header76_hex": h.bytes()[:76].hex(), "target_hex": target.hex(), "hashes": hashes,
+           "threads": threads, "backend": o.backend_name(), "seconds": round(dt, 1),
+           "shares": [{"nonce": s.nonce, "hash": s.hash.hex()} for s in shares]}
+    with open(os.path.join(HERE, f"config2_full_scan_header{index}.json"), "w") as f:
+        json.dump(doc, f, indent=1)
+    print(f"config2_full_scan_header{index}.json:", doc["shares"], f"{hashes / dt / 1e6:.1f} MH/s")
+
+
 def windows():
     doc = {"what": "dense-hit windows of the BASELINE workloads, from the CPU oracle", "cases": []}
     easy = o.target_from_difficulty(2.0 ** -16)
@@ -78,6 +97,9 @@ def windows():
 
 
 if __name__ == "__main__":
+    if "--synthetic" in sys.argv:
+        full_synthetic(int(sys.argv[sys.argv.index("--synthetic") + 1]))
+        sys.exit(0)
     windows()
     if "--full" in sys.argv:
         full_genesis()

@@ -155,6 +155,40 @@ def test_full_nonce_range_genesis(miner, golden):
     assert [(s.nonce, s.hash.hex()) for s in r.shares] == [(x["nonce"], x["hash"]) for x in g["shares"]]
 
 
+def test_config2_full_range_matches_the_cpu_full_scan(miner, golden):
+    """Completeness at FULL range beyond genesis: synthetic header 1 of configs[1], all 2^32
+    nonces at difficulty 1, against the CPU oracle's own full scan (committed fixture)."""
+    import json
+    p = os.path.join(os.path.dirname(__file__), "golden", "config2_full_scan_header1.json")
+    if not os.path.exists(p):
+        pytest.skip("config2_full_scan_header1.json not generated")
+    g = json.load(open(p))
+    f = W.config2_fields(g["index"])
+    assert mheader(miner, f).bytes()[:76].hex() == g["header76_hex"]
+    r = miner.scan(miner.Work(header=mheader(miner, f), target=bytes.fromhex(g["target_hex"])))
+    assert r.hashes == g["hashes"] == 1 << 32
+    assert [(s.nonce, s.hash.hex()) for s in r.shares] == [(x["nonce"], x["hash"]) for x in g["shares"]]
+
+
+def test_all_257_headers_stratified_completeness(miner, oracle):
+    """configs[1], every header: a 2^20 window at difficulty 2^-16 (dense hits) in one burst,
+    share sets identical to the CPU oracle's (SURVEY §8d stratified completeness)."""
+    t = oracle.target_from_difficulty(2.0 ** -16)
+    hdrs = [mheader(miner, W.config2_fields(i)) for i in range(W.CONFIG2_HEADERS)]
+    first, count = 0x7C000000, 1 << 20
+    r = miner.scan_headers(hdrs, t, first, count)
+    assert r.launches == 257 and r.hashes == 257 << 20
+    by_header = {}
+    for s in r.shares:
+        by_header.setdefault(s.job_id, []).append((s.nonce, s.hash))
+    total = 0
+    for i in range(W.CONFIG2_HEADERS):
+        want, _, _ = oracle.grind(oheader(oracle, W.config2_fields(i)), t, first, count, threads=NCPU, midstate=True)
+        assert by_header.get(i, []) == [(s.nonce, s.hash) for s in want], i
+        total += len(want)
+    assert total == r.found and total > 3000
+
+
 def test_config2_headers_full_range_soundness(miner, oracle):
     """configs[1] (subset): full nonce range at difficulty 1 on synthetic headers.
     Soundness bit-exact: every share re-hashed by the oracle meets the target."""
@@ -474,6 +508,24 @@ def test_two_workers_partition_the_version_space(miner, oracle):
                             device=g % ndev).shares
     assert sorted((s.version, s.nonce, s.hash) for s in parts) == sorted((s.version, s.nonce, s.hash) for s in whole.shares)
     assert len(whole.shares) > 20
+
+
+def test_device_telemetry_feeds_joules_per_terahash(miner):
+    """Observability parity: power / clock via NVML while the device hashes."""
+    from otedama_b200 import hal
+    dev = hal.CudaDriver().enumerate()[0]
+    f = W.config2_fields(30)
+    with miner.Worker() as w:
+        w.set_work(miner.Work(header=mheader(miner, f), target=miner.target_from_difficulty(1.0), repeat=True))
+        time.sleep(1.0)
+        power, mhz, temp = dev.telemetry()
+        h0, t0 = w.stats().hashes_total, time.time()
+        time.sleep(1.0)
+        rate = (w.stats().hashes_total - h0) / (time.time() - t0)
+    assert power > 50 and 500 < mhz < 3000 and temp > 0
+    assert rate > 1e9
+    jpth = power / (rate / 1e12)
+    assert 1e3 < jpth < 1e6, jpth     # ~55 kJ/TH at ~500 W and ~9 GH/s
 
 
 def test_int_peak_microbenchmark_runs(miner):
