@@ -38,6 +38,10 @@ extern "C" {
 /* Last error message of the calling thread ("" if none). Never NULL. */
 const char* otd_last_error(void);
 int otd_abi_version(void);
+/* sizeof() of the public structs as this library was compiled, so a binding can
+ * check its own layout: 0 otd_device_info_t, 1 otd_header_t, 2 otd_work_t,
+ * 3 otd_share_t, 4 otd_worker_config_t, 5 otd_stats_t, 6 otd_telemetry_t; -1 otherwise. */
+int otd_abi_struct_size(int which);
 
 /* ---------------------------------------------------------------- devices --
  * Replaces hal.Driver.Enumerate / hal.Device.Identity / Capabilities

@@ -55,11 +55,18 @@ def _compile(src, out, defines, log):
     return out
 
 
+STAMP_PATH = LIB_PATH + ".srchash"
+
+
+def source_hash() -> str:
+    return _digest(HEADERS + [MAIN_SRC, VARIANT_SRC], " ".join(NVCC_FLAGS))
+
+
 def needs_build() -> bool:
-    if not os.path.exists(LIB_PATH):
+    """Content based (not mtime based): snapshots and checkouts shuffle mtimes."""
+    if not os.path.exists(LIB_PATH) or not os.path.exists(STAMP_PATH):
         return True
-    t = os.path.getmtime(LIB_PATH)
-    return any(os.path.getmtime(d) > t for d in HEADERS + [MAIN_SRC, VARIANT_SRC])
+    return open(STAMP_PATH).read().strip() != source_hash()
 
 
 def build(force: bool = False, verbose: bool = False, jobs: int = 0) -> str:
@@ -92,6 +99,8 @@ def build(force: bool = False, verbose: bool = False, jobs: int = 0) -> str:
         fh.write("\n".join(log))
     if proc.returncode != 0:
         raise RuntimeError("link failed:\n" + proc.stdout + proc.stderr)
+    with open(STAMP_PATH, "w") as fh:
+        fh.write(source_hash() + "\n")
     if verbose:
         print("\n".join(log))
     return LIB_PATH

@@ -79,6 +79,7 @@ _NAMES32 = (c_char * 32)
 _SIGS = {
     "otd_last_error": (c_char_p, []),
     "otd_abi_version": (c_int, []),
+    "otd_abi_struct_size": (c_int, [c_int]),
     "otd_device_count": (c_int, []),
     "otd_device_info": (c_int, [c_int, POINTER(DeviceInfo)]),
     "otd_device_telemetry": (c_int, [c_int, POINTER(CTelemetry)]),

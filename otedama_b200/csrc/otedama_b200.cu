@@ -50,6 +50,19 @@ static int fail(int code, const std::string& msg)
 
 extern "C" const char* otd_last_error(void) { return g_last_error.c_str(); }
 extern "C" int otd_abi_version(void) { return OTD_ABI_VERSION; }
+extern "C" int otd_abi_struct_size(int which)
+{
+    switch (which) {
+        case 0: return (int)sizeof(otd_device_info_t);
+        case 1: return (int)sizeof(otd_header_t);
+        case 2: return (int)sizeof(otd_work_t);
+        case 3: return (int)sizeof(otd_share_t);
+        case 4: return (int)sizeof(otd_worker_config_t);
+        case 5: return (int)sizeof(otd_stats_t);
+        case 6: return (int)sizeof(otd_telemetry_t);
+        default: return -1;
+    }
+}
 
 // ----------------------------------------------------------------- devices --
 extern "C" int otd_device_count(void)

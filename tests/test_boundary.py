@@ -48,6 +48,11 @@ def test_product_never_uses_the_oracle():
 
 def test_struct_layouts_match_the_header(product):
     from otedama_b200 import capi
+    L = capi.lib()
+    for which, cls in enumerate((capi.DeviceInfo, capi.CHeader, capi.CWork, capi.CShare, capi.CWorkerConfig,
+                                 capi.CStats, capi.CTelemetry)):
+        assert L.otd_abi_struct_size(which) == ctypes.sizeof(cls), cls.__name__
+    assert L.otd_abi_struct_size(99) == -1
     assert ctypes.sizeof(capi.CHeader) == 80
     assert ctypes.sizeof(capi.CShare) == 80
     assert ctypes.sizeof(capi.CWorkerConfig) == 16

@@ -155,19 +155,24 @@ def test_full_nonce_range_genesis(miner, golden):
     assert [(s.nonce, s.hash.hex()) for s in r.shares] == [(x["nonce"], x["hash"]) for x in g["shares"]]
 
 
-def test_config2_full_range_matches_the_cpu_full_scan(miner, golden):
-    """Completeness at FULL range beyond genesis: synthetic header 1 of configs[1], all 2^32
-    nonces at difficulty 1, against the CPU oracle's own full scan (committed fixture)."""
+def test_config2_full_range_matches_the_cpu_full_scans(miner):
+    """Completeness at FULL range beyond genesis: synthetic headers of configs[1], all 2^32
+    nonces at difficulty 1, against the CPU oracle's own full scans (committed fixtures,
+    tests/golden/config2_full_scan_header*.json) — one burst, one launch per header."""
+    import glob
     import json
-    p = os.path.join(os.path.dirname(__file__), "golden", "config2_full_scan_header1.json")
-    if not os.path.exists(p):
-        pytest.skip("config2_full_scan_header1.json not generated")
-    g = json.load(open(p))
-    f = W.config2_fields(g["index"])
-    assert mheader(miner, f).bytes()[:76].hex() == g["header76_hex"]
-    r = miner.scan(miner.Work(header=mheader(miner, f), target=bytes.fromhex(g["target_hex"])))
-    assert r.hashes == g["hashes"] == 1 << 32
-    assert [(s.nonce, s.hash.hex()) for s in r.shares] == [(x["nonce"], x["hash"]) for x in g["shares"]]
+    paths = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "config2_full_scan_header*.json")))
+    if not paths:
+        pytest.skip("no config2_full_scan_header*.json fixture")
+    docs = [json.load(open(p)) for p in paths]
+    hdrs = [mheader(miner, W.config2_fields(g["index"])) for g in docs]
+    for h, g in zip(hdrs, docs):
+        assert h.bytes()[:76].hex() == g["header76_hex"] and g["hashes"] == 1 << 32
+    r = miner.scan_headers(hdrs, bytes.fromhex(docs[0]["target_hex"]))
+    assert r.hashes == len(docs) << 32
+    for i, g in enumerate(docs):
+        got = [(s.nonce, s.hash.hex()) for s in r.shares if s.job_id == i]
+        assert got == [(x["nonce"], x["hash"]) for x in g["shares"]], g["index"]
 
 
 def test_all_257_headers_stratified_completeness(miner, oracle):
