@@ -127,7 +127,7 @@ typedef struct {
     uint32_t version_begin, version_count, version_stride;
     /* Stratum V1 coinbase: coinb1 NULL = off (header.merkle_root is used).
      * coinbase = coinb1 || extranonce1 || extranonce2 || coinb2, extranonce2 =
-     * little-endian counter of extranonce2_size (<= 8) bytes, value
+     * little-endian counter of extranonce2_size (<= 16; bytes past the 8th are zero) bytes, value
      * e = extranonce2_begin + i*extranonce2_stride, i in [0, extranonce2_count).
      * merkle_branches = n_branches * 32 bytes.  Buffers are copied. */
     const uint8_t* coinb1;
@@ -237,8 +237,9 @@ int otd_scan(int device_index, const otd_work_t* work, int kernel_variant, otd_s
  * synthetic headers): header i of the batch is searched over the nonce window
  * against `target`; every launch is queued between one pair of CUDA events with
  * no host synchronisation in between (*device_ms is that span).  Shares carry the
- * header's batch index in job_id and come back sorted by (index, nonce).
- * Returns the number of shares written. */
+ * header's batch index in job_id and come back sorted by (index, nonce).  The
+ * whole burst shares one device ring of 65536 entries: more shares than that are
+ * dropped and show up only in *n_found.  Returns the number of shares written. */
 int otd_scan_headers(int device_index, const otd_header_t* headers, uint32_t n_headers,
                      const uint8_t target[32], uint32_t nonce_begin, uint64_t nonce_count,
                      int kernel_variant, otd_share_t* out, uint32_t max_shares, uint64_t* n_found,

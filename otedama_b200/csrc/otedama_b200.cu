@@ -460,13 +460,12 @@ static int num_usable_variants()
     }();
     return n;
 }
-#define kNumVariants (num_usable_variants())
 
 extern "C" int otd_scan_variants(char (*names)[32], int max_names)
 {
     if (names)
-        for (int i = 0; i < kNumVariants && i < max_names; i++) snprintf(names[i], 32, "%s", kVariants[i].name);
-    return kNumVariants;
+        for (int i = 0; i < num_usable_variants() && i < max_names; i++) snprintf(names[i], 32, "%s", kVariants[i].name);
+    return num_usable_variants();
 }
 extern "C" int otd_scan_default_variant(void) { return kDefaultVariant; }
 
@@ -772,7 +771,7 @@ class Engine {
             const std::function<bool()>& aborted, RunStats& rs)
     {
         if (!ready) return fail(OTD_EINVAL, "engine not initialised");
-        if (variant < 0 || variant >= kNumVariants) variant = kDefaultVariant;
+        if (variant < 0 || variant >= num_usable_variants()) variant = kDefaultVariant;
         const ScanVariant& kv = kVariants[variant];
         if (launch_log2 == 0) launch_log2 = 32;
         launch_log2 = std::min(32u, std::max(16u, launch_log2));
@@ -914,7 +913,7 @@ extern "C" int otd_scan_headers(int device_index, const otd_header_t* headers, u
     int rc = pool_engine(device_index, &eng, &lock);
     if (rc) return rc;
     std::lock_guard<std::mutex> g(*lock);
-    if (kernel_variant < 0 || kernel_variant >= kNumVariants) kernel_variant = kDefaultVariant;
+    if (kernel_variant < 0 || kernel_variant >= num_usable_variants()) kernel_variant = kDefaultVariant;
     const ScanVariant& kv = kVariants[kernel_variant];
     uint32_t tgt[8];
     for (int i = 0; i < 8; i++) tgt[i] = get_le32(target + 4 * i);
@@ -1335,7 +1334,7 @@ extern "C" int otd_scan_noalloc(int device_index, const otd_work_t* work, int ke
         return fail(OTD_EINVAL, "nonce window exceeds 2^32");
     int rc = check_device(device_index);
     if (rc) return rc;
-    if (kernel_variant < 0 || kernel_variant >= kNumVariants) kernel_variant = kDefaultVariant;
+    if (kernel_variant < 0 || kernel_variant >= num_usable_variants()) kernel_variant = kDefaultVariant;
     const ScanVariant& kv = kVariants[kernel_variant];
 
     std::lock_guard<std::mutex> g(g_noalloc_mu);
