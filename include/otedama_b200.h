@@ -176,6 +176,37 @@ int otd_work_from_v2_job(uint32_t job_id, uint32_t channel_id, uint32_t version,
 int otd_work_from_v1_job(const char* job_id, uint32_t channel_id, const uint8_t merkle_root[32], uint32_t ntime,
                          uint32_t nbits, double difficulty, otd_work_t* work);
 
+/* Stratum V1 mining.notify -> device work unit with on-device extranonce2 rolling
+ * (north_star).  The reference's parseNotify keeps job id, prevhash,
+ * version, nbits, ntime and DISCARDS coinb1 / coinb2 / merkle_branch
+ * (internal/poolproto/stratumv1/parse.go:33-93), so this follows the public
+ * Stratum V1 conventions ("parity unpinned"):
+ *   params = [job_id, prevhash, coinb1, coinb2, merkle_branch[], version, nbits, ntime, clean_jobs]
+ *   - prevhash: 64 hex chars, eight 4-byte words each byte-swapped with respect to
+ *     header order (header bytes = each word reversed);
+ *   - version / nbits / ntime: big-endian hex of the u32 header fields;
+ *   - coinbase = coinb1 || extranonce1 || extranonce2 || coinb2 (hex decoded).
+ * job_id is parsed like the reference's applyJob (Sscanf "%d", run.go:1345-1348);
+ * the share target comes from v1JobTarget(nbits, difficulty).  The decoded bytes
+ * the work points to are placed in `scratch` (caller-owned; must outlive the use
+ * of *work; otd_worker_set_work / otd_scan copy them).  Returns OTD_OK, or
+ * OTD_ERANGE with *scratch_needed set when scratch_len is too small. */
+typedef struct {
+    const char* job_id;
+    const char* prevhash_hex;
+    const char* coinb1_hex;
+    const char* coinb2_hex;
+    const char* const* merkle_branch_hex; /* n_branches strings of 64 hex chars */
+    uint32_t n_branches;
+    const char* version_hex;
+    const char* nbits_hex;
+    const char* ntime_hex;
+    int32_t clean_jobs;
+} otd_v1_notify_t;
+int otd_work_from_v1_notify(const otd_v1_notify_t* notify, const char* extranonce1_hex,
+                            uint32_t extranonce2_size, double difficulty, uint32_t channel_id,
+                            otd_work_t* work, uint8_t* scratch, size_t scratch_len, size_t* scratch_needed);
+
 /* ----------------------------------------------------------------- worker --
  * One worker per device: the GPU counterpart of *miner.Worker
  * (internal/miner/worker.go:91-212), constructed by engine.startMinerWorkers

@@ -330,3 +330,15 @@ def bip320_version_py(base: int, mask: int, k: int) -> int:
                 v |= 1 << bit
             k >>= 1
     return v
+
+
+def v1_header(params, extranonce1: bytes, extranonce2: bytes) -> Header:
+    """UNPINNED: the header a Stratum V1 miner hashes for mining.notify `params`
+    ([job_id, prevhash, coinb1, coinb2, merkle_branch, version, nbits, ntime, clean]) —
+    public convention: prevhash words byte-swapped, big-endian hex scalars."""
+    _, prevhash, coinb1, coinb2, branch, version, nbits, ntime = params[:8]
+    pw = bytes.fromhex(prevhash)
+    prev = b"".join(pw[4 * i:4 * i + 4][::-1] for i in range(8))
+    root = v1_merkle_root_py(bytes.fromhex(coinb1), extranonce1, extranonce2, bytes.fromhex(coinb2),
+                             [bytes.fromhex(b) for b in branch])
+    return Header(int(version, 16), prev, root, int(ntime, 16), int(nbits, 16), 0)

@@ -56,6 +56,12 @@ class CWork(Structure):
                 ("extranonce2_count", c_uint64), ("extranonce2_stride", c_uint64)]
 
 
+class CV1Notify(Structure):
+    _fields_ = [("job_id", c_char_p), ("prevhash_hex", c_char_p), ("coinb1_hex", c_char_p), ("coinb2_hex", c_char_p),
+                ("merkle_branch_hex", POINTER(c_char_p)), ("n_branches", c_uint32), ("version_hex", c_char_p),
+                ("nbits_hex", c_char_p), ("ntime_hex", c_char_p), ("clean_jobs", c_int32)]
+
+
 class CShare(Structure):
     _fields_ = [("channel_id", c_uint32), ("job_id", c_uint32), ("nonce", c_uint32), ("ntime", c_uint32),
                 ("version", c_uint32), ("hash", c_uint8 * 32), ("extranonce2", c_uint64),
@@ -95,6 +101,8 @@ _SIGS = {
     "otd_work_from_v2_job": (c_int, [c_uint32, c_uint32, c_uint32, c_char_p, c_char_p, c_uint32, c_uint32, c_char_p,
                                      POINTER(CWork)]),
     "otd_work_from_v1_job": (c_int, [c_char_p, c_uint32, c_char_p, c_uint32, c_uint32, c_double, POINTER(CWork)]),
+    "otd_work_from_v1_notify": (c_int, [POINTER(CV1Notify), c_char_p, c_uint32, c_double, c_uint32, POINTER(CWork),
+                                        c_char_p, c_size_t, POINTER(c_size_t)]),
     "otd_worker_create": (c_void_p, [c_int, POINTER(CWorkerConfig)]),
     "otd_worker_set_work": (c_int64, [c_void_p, POINTER(CWork)]),
     "otd_worker_poll_shares": (c_int, [c_void_p, POINTER(CShare), c_int, c_int]),

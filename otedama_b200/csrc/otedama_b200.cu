@@ -435,6 +435,85 @@ extern "C" int otd_work_from_v1_job(const char* job_id, uint32_t channel_id, con
     return OTD_OK;
 }
 
+static int hex_nibble(char c)
+{
+    if (c >= '0' && c <= '9') return c - '0';
+    if (c >= 'a' && c <= 'f') return c - 'a' + 10;
+    if (c >= 'A' && c <= 'F') return c - 'A' + 10;
+    return -1;
+}
+// decodes the whole string; returns the byte count or -1
+static long hex_decode(const char* s, uint8_t* out, size_t cap)
+{
+    const size_t n = strlen(s);
+    if (n % 2) return -1;
+    if (n / 2 > cap) return -2;
+    for (size_t i = 0; i < n / 2; i++) {
+        const int a = hex_nibble(s[2 * i]), b = hex_nibble(s[2 * i + 1]);
+        if (a < 0 || b < 0) return -1;
+        out[i] = (uint8_t)(a << 4 | b);
+    }
+    return (long)(n / 2);
+}
+static int hex_u32_be(const char* s, uint32_t* out)
+{
+    uint8_t b[4];
+    if (!s || strlen(s) != 8 || hex_decode(s, b, 4) != 4) return -1;
+    *out = (uint32_t)b[0] << 24 | (uint32_t)b[1] << 16 | (uint32_t)b[2] << 8 | b[3];
+    return 0;
+}
+
+extern "C" int otd_work_from_v1_notify(const otd_v1_notify_t* n, const char* extranonce1_hex,
+                                       uint32_t extranonce2_size, double difficulty, uint32_t channel_id,
+                                       otd_work_t* work, uint8_t* scratch, size_t scratch_len, size_t* scratch_needed)
+{
+    if (!n || !work || !n->job_id || !n->prevhash_hex || !n->coinb1_hex || !n->coinb2_hex || !n->version_hex ||
+        !n->nbits_hex || !n->ntime_hex || (n->n_branches && !n->merkle_branch_hex))
+        return fail(OTD_EINVAL, "otd_work_from_v1_notify: NULL field");
+    if (!extranonce1_hex) extranonce1_hex = "";
+    if (extranonce2_size > 16) return fail(OTD_EINVAL, "otd_work_from_v1_notify: extranonce2_size > 16");
+    if (n->n_branches > 64) return fail(OTD_EINVAL, "otd_work_from_v1_notify: more than 64 merkle branches");
+    const size_t l1 = strlen(n->coinb1_hex) / 2, l2 = strlen(n->coinb2_hex) / 2, le1 = strlen(extranonce1_hex) / 2;
+    const size_t need = l1 + le1 + l2 + 32 * (size_t)n->n_branches;
+    if (scratch_needed) *scratch_needed = need;
+    if (need > scratch_len || (need && !scratch))
+        return fail(OTD_ERANGE, "otd_work_from_v1_notify: scratch too small (" + std::to_string(need) + " bytes needed)");
+    uint32_t version, nbits, ntime;
+    if (hex_u32_be(n->version_hex, &version) || hex_u32_be(n->nbits_hex, &nbits) || hex_u32_be(n->ntime_hex, &ntime))
+        return fail(OTD_EINVAL, "otd_work_from_v1_notify: version / nbits / ntime must be 8 hex characters");
+    uint8_t prev_wire[32];
+    if (strlen(n->prevhash_hex) != 64 || hex_decode(n->prevhash_hex, prev_wire, 32) != 32)
+        return fail(OTD_EINVAL, "otd_work_from_v1_notify: prevhash must be 64 hex characters");
+    otd_work_t w;
+    uint8_t zero[32] = {0};
+    int rc = otd_work_from_v1_job(n->job_id, channel_id, zero, ntime, nbits, difficulty, &w);  // id, target, time, bits
+    if (rc) return rc;
+    w.header.version = version;
+    for (int wi = 0; wi < 8; wi++)      // each 4-byte word reversed -> header (internal) byte order
+        for (int b = 0; b < 4; b++) w.header.prev_hash[4 * wi + b] = prev_wire[4 * wi + 3 - b];
+    uint8_t* p = scratch;
+    if (hex_decode(n->coinb1_hex, p, l1) != (long)l1) return fail(OTD_EINVAL, "otd_work_from_v1_notify: coinb1 is not hex");
+    w.coinb1 = p; w.coinb1_len = (uint32_t)l1; p += l1;
+    if (hex_decode(extranonce1_hex, p, le1) != (long)le1) return fail(OTD_EINVAL, "otd_work_from_v1_notify: extranonce1 is not hex");
+    w.extranonce1 = p; w.extranonce1_len = (uint32_t)le1; p += le1;
+    if (hex_decode(n->coinb2_hex, p, l2) != (long)l2) return fail(OTD_EINVAL, "otd_work_from_v1_notify: coinb2 is not hex");
+    w.coinb2 = p; w.coinb2_len = (uint32_t)l2; p += l2;
+    w.merkle_branches = p;
+    w.n_branches = n->n_branches;
+    for (uint32_t i = 0; i < n->n_branches; i++) {
+        if (!n->merkle_branch_hex[i] || strlen(n->merkle_branch_hex[i]) != 64 || hex_decode(n->merkle_branch_hex[i], p, 32) != 32)
+            return fail(OTD_EINVAL, "otd_work_from_v1_notify: merkle branch " + std::to_string(i) + " must be 64 hex characters");
+        p += 32;
+    }
+    w.extranonce2_size = extranonce2_size;
+    w.extranonce2_begin = 0;
+    // every value the field can hold, capped at 2^40 values (x 2^32 nonces each: far beyond any job's life)
+    w.extranonce2_count = extranonce2_size >= 5 ? (1ull << 40) : (1ull << (8 * extranonce2_size));
+    w.extranonce2_stride = 1;
+    *work = w;
+    return OTD_OK;
+}
+
 // ------------------------------------------------------------ scan variants --
 struct ScanVariant {
     const char* name;

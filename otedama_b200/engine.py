@@ -87,3 +87,33 @@ def apply_job(workers: Iterable, job: Job, chan_id: int, difficulty: float) -> N
     w = work_from_v1_job(job, chan_id, difficulty)
     for wr in workers:
         wr.set_work(w)
+
+
+def work_from_v1_notify(params, extranonce1_hex: str, extranonce2_size: int, difficulty: float, chan_id: int = 0,
+                        extranonce2_begin: int = 0, extranonce2_count: int = 0, extranonce2_stride: int = 1) -> miner.Work:
+    """mining.notify params [job_id, prevhash, coinb1, coinb2, merkle_branch, version, nbits, ntime, clean]
+    -> a Work whose extranonce2 is rolled on the device (otd_work_from_v1_notify)."""
+    job_id, prevhash, coinb1, coinb2, branch, version, nbits, ntime, clean = params[:9]
+    arr = (ctypes.c_char_p * max(1, len(branch)))(*[b.encode() for b in branch])
+    n = capi.CV1Notify(str(job_id).encode(), prevhash.encode(), coinb1.encode(), coinb2.encode(), arr, len(branch),
+                       version.encode(), nbits.encode(), ntime.encode(), int(bool(clean)))
+    need = ctypes.c_size_t()
+    cw = CWork()
+    scratch = ctypes.create_string_buffer(len(coinb1) // 2 + len(coinb2) // 2 + len(extranonce1_hex) // 2 + 32 * len(branch) + 1)
+    rc = lib().otd_work_from_v1_notify(ctypes.byref(n), extranonce1_hex.encode(), extranonce2_size, float(difficulty),
+                                       chan_id, ctypes.byref(cw), scratch, len(scratch), ctypes.byref(need))
+    if rc < 0:
+        raise EngineError(capi.last_error())
+    raw = scratch.raw
+    l1, le1, l2 = cw.coinb1_len, cw.extranonce1_len, cw.coinb2_len
+    w = _work_from_c(cw)
+    w.coinb1 = raw[:l1]
+    w.extranonce1 = raw[l1:l1 + le1]
+    w.coinb2 = raw[l1 + le1:l1 + le1 + l2]
+    base = l1 + le1 + l2
+    w.merkle_branches = [raw[base + 32 * i:base + 32 * i + 32] for i in range(cw.n_branches)]
+    w.extranonce2_size = cw.extranonce2_size
+    w.extranonce2_begin = extranonce2_begin
+    w.extranonce2_count = extranonce2_count or cw.extranonce2_count
+    w.extranonce2_stride = extranonce2_stride
+    return w

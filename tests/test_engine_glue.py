@@ -89,3 +89,61 @@ def test_update_work_share_echoes_version_and_ntime_on_the_gpu(eng):
         s = w.poll_shares(1, 3000)
         assert s, "no share within 3s at the easiest share target"
         assert (s[0].job_id, s[0].version, s[0].ntime, s[0].channel_id) == (42, 0x20000004, 0x60000000, 1)
+
+
+# the reference's own (syntactic) notify fixture, internal/poolproto/stratumv1/stratumv1_test.go:71-81
+REF_NOTIFY = ["60", "4d16b6f85af6e2198f44ae2a6de67f78487ae5611b77c6c0440b921e00000000",
+              "01000000010000000000000000000000000000000000000000000000000000000000000000ffffffff20",
+              "ffffffff0100f2052a010000004341041b0e8c2567c12536aa13357b79a073dc4444acb83c4ec7a0e2f99dd7457516c5817242da796924ca4e99947d087fedf9ce467cb9f7c6287078f801df276fdf84ac00000000",
+              [], "00000002", "1d00ffff", "68d36c5e", True]
+
+
+def test_v1_notify_to_work_unit(eng, oracle, golden):
+    engine, miner = eng
+    rv = golden["reference_vectors"]["v1_notify_fixture"]
+    assert REF_NOTIFY[2] == rv["coinb1"] and REF_NOTIFY[3] == rv["coinb2"]
+    w = engine.work_from_v1_notify(REF_NOTIFY, "deadbeef", 4, 1024.0, chan_id=3)
+    # the fields the reference's parseNotify also extracts (parse.go:77-90)
+    assert (w.job_id, w.channel_id, w.header.version, w.nbits, w.header.bits, w.header.time) == \
+           (60, 3, 2, 0x1D00FFFF, 0x1D00FFFF, 0x68D36C5E)
+    assert w.target == oracle.target_from_difficulty(1024.0)        # v1JobTarget with set_difficulty 1024
+    want = oracle.v1_header(REF_NOTIFY, bytes.fromhex("deadbeef"), b"\x00" * 4)
+    assert w.header.prev_hash == want.prev_hash and w.header.prev_hash.endswith(b"\x00" * 4)
+    assert (w.coinb1.hex(), w.coinb2.hex(), w.extranonce1.hex(), list(w.merkle_branches)) == \
+           (REF_NOTIFY[2], REF_NOTIFY[3], "deadbeef", [])
+    assert (w.extranonce2_size, w.extranonce2_count) == (4, 1 << 32)
+    assert engine.work_from_v1_notify(REF_NOTIFY, "", 8, 0).extranonce2_count == 1 << 40
+    # with branches, random content: C decoder vs the Python restatement
+    import random
+    rnd = random.Random(5)
+    params = ["7", rnd.randbytes(32).hex(), rnd.randbytes(41).hex(), rnd.randbytes(77).hex(),
+              [rnd.randbytes(32).hex() for _ in range(12)], "20000000", "1d00ffff", "60000000", False]
+    w = engine.work_from_v1_notify(params, "0a0b", 8, 0, extranonce2_begin=5, extranonce2_count=3)
+    oh = oracle.v1_header(params, bytes.fromhex("0a0b"), (5).to_bytes(8, "little"))
+    assert (w.header.version, w.header.prev_hash, w.header.time, w.header.bits) == (oh.version, oh.prev_hash, oh.time, oh.bits)
+    assert [b.hex() for b in w.merkle_branches] == params[4] and w.target == oracle.target_from_nbits(0x1D00FFFF)
+    for bad in (["x"] + params[1:], params[:1] + ["00"] + params[2:], params[:5] + ["2000000"] + params[6:],
+                params[:4] + [["zz" * 32]] + params[5:], params[:2] + ["abc"] + params[3:]):
+        with pytest.raises(engine.EngineError):
+            engine.work_from_v1_notify(bad, "", 4, 0)
+
+
+@pytest.mark.gpu
+def test_v1_notify_work_unit_scans_like_the_oracle(eng, oracle):
+    """notify -> work unit -> device (K3 roll + K2 midstate + K1 scan) vs the oracle's header."""
+    engine, miner = eng
+    import os
+    import random
+    rnd = random.Random(9)
+    params = ["12", rnd.randbytes(32).hex(), rnd.randbytes(58).hex(), rnd.randbytes(107).hex(),
+              [rnd.randbytes(32).hex() for _ in range(12)], "20000000", "1d00ffff", "60000000", True]
+    w = engine.work_from_v1_notify(params, "deadbeef", 8, 2.0 ** -18, extranonce2_begin=100, extranonce2_count=6)
+    w.nonce_count = 1 << 16
+    r = miner.scan(w)
+    want = []
+    for e in range(100, 106):
+        oh = oracle.v1_header(params, bytes.fromhex("deadbeef"), e.to_bytes(8, "little"))
+        sh, _, _ = oracle.grind(oh, w.target, 0, 1 << 16, threads=os.cpu_count() or 1)
+        want += [(e, s.nonce, s.hash) for s in sh]
+    assert sorted((s.extranonce2, s.nonce, s.hash) for s in r.shares) == sorted(want) and len(want) > 10
+    assert all(s.job_id == 12 and s.ntime == 0x60000000 and s.version == 0x20000000 for s in r.shares)
