@@ -26,6 +26,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--gpus", type=int, default=1)
 ap.add_argument("--seconds", type=float, default=20.0)
 ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "configs.json"))
+ap.add_argument("--only", default="", help="comma list of 2,3,4 (BASELINE config indices) to run; default all")
 a = ap.parse_args()
 G = min(a.gpus, capi.check(capi.lib().otd_device_count()))
 diff1 = miner.target_from_difficulty(1.0)
@@ -61,6 +62,7 @@ def run(name, works, check_share):
     return res
 
 
+only = set(a.only.split(",")) if a.only else {"2", "3", "4"}
 results = []
 # ---- config 3 / 5: V1 coinbase, extranonce2 e -> GPU e mod G ----
 c3 = W.config3_v1()
@@ -80,7 +82,8 @@ def check_v1(s):
     return o.hash_header(h) == s.hash and o.less_or_equal(s.hash, diff1) and s.version == c3["version"]
 
 
-results.append(run("configs[2] V1 notify replay, extranonce2 rolled on device, 1 GPU", [v1_work(0, 1)], check_v1))
+if "2" in only:
+    results.append(run("configs[2] V1 notify replay, extranonce2 rolled on device, 1 GPU", [v1_work(0, 1)], check_v1))
 
 # ---- config 4: BIP-320 version rolling, version index k -> GPU k mod G ----
 c4 = W.config4_v2()
@@ -98,8 +101,9 @@ def check_v2(s):
     return ok_bits and o.hash_header(h) == s.hash and o.less_or_equal(s.hash, diff1)
 
 
-results.append(run(f"configs[3] SV2 + BIP-320 version rolling, {G} GPU(s)", [v2_work(g, G) for g in range(G)], check_v2))
-if G > 1:
+if "3" in only:
+    results.append(run(f"configs[3] SV2 + BIP-320 version rolling, {G} GPU(s)", [v2_work(g, G) for g in range(G)], check_v2))
+if "4" in only and (G > 1 or a.only):
     results.append(run(f"configs[4] sustained sweep, extranonce2 sharded over {G} GPUs", [v1_work(g, G) for g in range(G)],
                        check_v1))
 os.makedirs(os.path.dirname(a.out), exist_ok=True)
