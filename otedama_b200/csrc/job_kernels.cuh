@@ -148,19 +148,28 @@ __global__ void hash_headers_kernel(const uint8_t* __restrict__ hdrs, unsigned l
 {
     const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const uint32_t* h = reinterpret_cast<const uint32_t*>(hdrs + 80ull * i);  // 80*i is 16B aligned
+    // 80-byte records are 16-byte aligned (cudaMalloc base, 80 = 5 x 16): five 128-bit loads per
+    // header through the read-only path, two 128-bit stores per digest.
+    const uint4* h4 = reinterpret_cast<const uint4*>(hdrs + 80ull * i);
+    uint32_t raw[20];
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        const uint4 v = __ldg(h4 + k);
+        raw[4 * k] = v.x; raw[4 * k + 1] = v.y; raw[4 * k + 2] = v.z; raw[4 * k + 3] = v.w;
+    }
     uint32_t w[16], st[8];
-    for (int k = 0; k < 16; k++) w[k] = bswap32(__ldg(h + k));
+    for (int k = 0; k < 16; k++) w[k] = bswap32(raw[k]);
     iv_init(st);
     compress(st, w);
-    for (int k = 0; k < 4; k++) w[k] = bswap32(__ldg(h + 16 + k));
+    for (int k = 0; k < 4; k++) w[k] = bswap32(raw[16 + k]);
     w[4] = 0x80000000u;
     for (int k = 5; k < 15; k++) w[k] = 0;
     w[15] = 0x280u;
     compress(st, w);
     sha256_of_digest(st);
-    uint32_t* o = reinterpret_cast<uint32_t*>(out + 32ull * i);
-    for (int k = 0; k < 8; k++) o[k] = bswap32(st[k]);
+    uint4* o4 = reinterpret_cast<uint4*>(out + 32ull * i);
+    o4[0] = make_uint4(bswap32(st[0]), bswap32(st[1]), bswap32(st[2]), bswap32(st[3]));
+    o4[1] = make_uint4(bswap32(st[4]), bswap32(st[5]), bswap32(st[6]), bswap32(st[7]));
 }
 
 #endif  // __CUDACC__
