@@ -77,7 +77,8 @@ def hash_headers(headers: Sequence[bytes], device: int = 0) -> List[bytes]:
         raise MinerError("every header must be 80 bytes")
     out = ctypes.create_string_buffer(32 * n)
     check(lib().otd_hash_headers(device, blob, n, out))
-    return [out.raw[32 * i:32 * i + 32] for i in range(n)]
+    raw = out.raw  # one copy; .raw re-copies the whole buffer on every access
+    return [raw[32 * i:32 * i + 32] for i in range(n)]
 
 
 def hash_header(h: Header, device: int = 0) -> bytes:
@@ -383,7 +384,8 @@ def prepare_instances(work: Work, first: int, n: int, device: int = 0) -> List[I
     en2 = (ctypes.c_uint64 * n)()
     check(lib().otd_prepare_instances(device, ctypes.byref(cw), first, n, roots, vers, en2, mids))
     del keep
-    return [Instance(roots.raw[32 * i:32 * i + 32], vers[i], en2[i], mids.raw[32 * i:32 * i + 32]) for i in range(n)]
+    r, m = roots.raw, mids.raw
+    return [Instance(r[32 * i:32 * i + 32], vers[i], en2[i], m[32 * i:32 * i + 32]) for i in range(n)]
 
 
 def int_peak(mode: int, device: int = 0, iters: int = 2048):
