@@ -101,6 +101,9 @@ enum : unsigned {
     KN_BS1 = 256u,   // Sigma1: two of three rotations via IMAD.WIDE
     KN_BS0 = 512u,   // Sigma0: two of three rotations via IMAD.WIDE
     KN_T1X = 1024u,  // t1 = IMAD(IADD3(IMAD(h,1,W), Sigma1, K), 1, Ch): one ALU add, no IMAD with an immediate
+    KN_SP = 4096u,   // register+register adds of the specialised parts (first schedule words, rounds 4..6) as IMAD
+                     // (adds with a constant-bank or immediate operand stay on the ALU: an IMAD with a
+                     //  non-register addend raises dispatch stalls, measured with c[] operands as well)
     KN_COMPACT = 2048u,  // partially rolled body (scan_core_compact): the three fully generic 16-round blocks
                          // share one loop body so the code stays well inside the instruction cache
 };
@@ -310,6 +313,19 @@ template <int V, unsigned KN> OTD_HD vw<V> vS1(const Ops<KN>& op, const vw<V>& x
     return r;
 }
 
+// adds of the specialised parts, placed by KN_SP / KN_CADD
+template <int V, unsigned KN> OTD_HD vw<V> padd(const Ops<KN>& op, const vw<V>& a, const vw<V>& b)
+{
+    vw<V> r;
+#pragma unroll
+    for (int i = 0; i < V; i++) r.x[i] = op.add_if(KN & KN_SP, a.x[i], b.x[i]);
+    return r;
+}
+template <int V, unsigned KN> OTD_HD vw<V> cadd(const Ops<KN>&, const vw<V>& a, uint32_t c)
+{
+    return a + c;  // job-constant / immediate addend: ALU
+}
+
 // 8 rounds starting at round index R with schedule words w[R..R+7] already final.
 #define OTD_R8(R, a, b, c, d, e, f, g, h)                                \
     rnd(op, a, b, c, d, e, f, g, h, w[(R) + 0], Kc((R) + 0));   \
@@ -339,15 +355,15 @@ OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
 
     // rounds 4..6: h and d are still job constants (k4/k5/k6 carry h + K + W)
     {
-        vw<V> t1 = vS1(op, e) + ch(e, f, g) + jc.k4;                  // round 4
-        vw<V> e5 = t1 + jc.c3;
-        vw<V> a5 = t1 + vS0(op, a) + maj(a, b, c);
-        t1 = vS1(op, e5) + ch(e5, e, f) + jc.k5;                      // round 5
-        vw<V> e6 = t1 + jc.b3;
-        vw<V> a6 = t1 + vS0(op, a5) + maj(a5, a, b);
-        t1 = vS1(op, e6) + ch(e6, e5, e) + jc.k6;                     // round 6
-        vw<V> e7 = t1 + jc.a3;
-        vw<V> a7 = t1 + vS0(op, a6) + maj(a6, a5, a);
+        vw<V> t1 = cadd(op, padd(op, vS1(op, e), ch(e, f, g)), jc.k4);                  // round 4
+        vw<V> e5 = cadd(op, t1, jc.c3);
+        vw<V> a5 = padd(op, padd(op, t1, vS0(op, a)), maj(a, b, c));
+        t1 = cadd(op, padd(op, vS1(op, e5), ch(e5, e, f)), jc.k5);                      // round 5
+        vw<V> e6 = cadd(op, t1, jc.b3);
+        vw<V> a6 = padd(op, padd(op, t1, vS0(op, a5)), maj(a5, a, b));
+        t1 = cadd(op, padd(op, vS1(op, e6), ch(e6, e5, e)), jc.k6);                     // round 6
+        vw<V> e7 = cadd(op, t1, jc.a3);
+        vw<V> a7 = padd(op, padd(op, t1, vS0(op, a6)), maj(a6, a5, a));
         // state entering round 7: (a7, a6, a5, a4, e7, e6, e5, e4)
         vw<V> a4 = a, e4 = e;
         a = a7; b = a6; c = a5; d = a4; e = e7; f = e6; g = e5; h = e4;
@@ -363,21 +379,21 @@ OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
     rnd(op, b, c, d, e, f, g, h, a, Kc(14));
     rnd(op, a, b, c, d, e, f, g, h, Kc(15) + 0x280u);
     // schedule words 18..33 (16, 17 are job constants)
-    w[18] = vs0(op, w3) + jc.c18;
-    w[19] = w3 + jc.c19;
+    w[18] = cadd(op, vs0(op, w3), jc.c18);
+    w[19] = cadd(op, w3, jc.c19);
     w[20] = vs1(op, w[18]) + 0x80000000u;
     w[21] = vs1(op, w[19]);
     w[22] = vs1(op, w[20]) + 0x280u;
-    w[23] = vs1(op, w[21]) + jc.w16;
-    w[24] = vs1(op, w[22]) + jc.w17;
-    w[25] = vs1(op, w[23]) + w[18];
-    w[26] = vs1(op, w[24]) + w[19];
-    w[27] = vs1(op, w[25]) + w[20];
-    w[28] = vs1(op, w[26]) + w[21];
-    w[29] = vs1(op, w[27]) + w[22];
-    w[30] = vs1(op, w[28]) + w[23] + ssig0(0x280u);
-    w[31] = vs1(op, w[29]) + w[24] + jc.c31;
-    w[32] = vs1(op, w[30]) + w[25] + jc.c32;
+    w[23] = cadd(op, vs1(op, w[21]), jc.w16);
+    w[24] = cadd(op, vs1(op, w[22]), jc.w17);
+    w[25] = padd(op, vs1(op, w[23]), w[18]);
+    w[26] = padd(op, vs1(op, w[24]), w[19]);
+    w[27] = padd(op, vs1(op, w[25]), w[20]);
+    w[28] = padd(op, vs1(op, w[26]), w[21]);
+    w[29] = padd(op, vs1(op, w[27]), w[22]);
+    w[30] = padd(op, vs1(op, w[28]), w[23]) + ssig0(0x280u);
+    w[31] = cadd(op, padd(op, vs1(op, w[29]), w[24]), jc.c31);
+    w[32] = cadd(op, padd(op, vs1(op, w[30]), w[25]), jc.c32);
     w[33] = sched(op, w[31], w[26], w[18], bc<V>(jc.w17));
 #pragma unroll
     for (int i = 34; i < 64; i++) w[i] = sched(op, w[i - 2], w[i - 7], w[i - 15], w[i - 16]);
@@ -409,25 +425,25 @@ OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
 
     // ---------------- hash 2 ----------------
     // message = digest of hash 1 (state + midstate), padding, length 256 bits
-    w[0] = h + jc.mid[0]; w[1] = a + jc.mid[1]; w[2] = b + jc.mid[2]; w[3] = c + jc.mid[3];
-    w[4] = d + jc.mid[4]; w[5] = e + jc.mid[5]; w[6] = f + jc.mid[6]; w[7] = g + jc.mid[7];
+    w[0] = cadd(op, h, jc.mid[0]); w[1] = cadd(op, a, jc.mid[1]); w[2] = cadd(op, b, jc.mid[2]); w[3] = cadd(op, c, jc.mid[3]);
+    w[4] = cadd(op, d, jc.mid[4]); w[5] = cadd(op, e, jc.mid[5]); w[6] = cadd(op, f, jc.mid[6]); w[7] = cadd(op, g, jc.mid[7]);
     // W8 = 0x80000000, W9..14 = 0, W15 = 0x100: written out so the zero terms vanish
-    w[16] = vs0(op, w[1]) + w[0];
-    w[17] = vs0(op, w[2]) + w[1] + ssig1(0x100u);
-    w[18] = vs1(op, w[16]) + vs0(op, w[3]) + w[2];
-    w[19] = vs1(op, w[17]) + vs0(op, w[4]) + w[3];
-    w[20] = vs1(op, w[18]) + vs0(op, w[5]) + w[4];
-    w[21] = vs1(op, w[19]) + vs0(op, w[6]) + w[5];
+    w[16] = padd(op, vs0(op, w[1]), w[0]);
+    w[17] = padd(op, vs0(op, w[2]), w[1]) + ssig1(0x100u);
+    w[18] = padd(op, padd(op, vs1(op, w[16]), vs0(op, w[3])), w[2]);
+    w[19] = padd(op, padd(op, vs1(op, w[17]), vs0(op, w[4])), w[3]);
+    w[20] = padd(op, padd(op, vs1(op, w[18]), vs0(op, w[5])), w[4]);
+    w[21] = padd(op, padd(op, vs1(op, w[19]), vs0(op, w[6])), w[5]);
     w[22] = sched(op, w[20], bc<V>(0x100u), w[7], w[6]);
-    w[23] = vs1(op, w[21]) + w[16] + w[7] + ssig0(0x80000000u);
-    w[24] = vs1(op, w[22]) + w[17] + 0x80000000u;
-    w[25] = vs1(op, w[23]) + w[18];
-    w[26] = vs1(op, w[24]) + w[19];
-    w[27] = vs1(op, w[25]) + w[20];
-    w[28] = vs1(op, w[26]) + w[21];
-    w[29] = vs1(op, w[27]) + w[22];
-    w[30] = vs1(op, w[28]) + w[23] + ssig0(0x100u);
-    w[31] = vs1(op, w[29]) + w[24] + vs0(op, w[16]) + 0x100u;
+    w[23] = padd(op, padd(op, vs1(op, w[21]), w[16]), w[7]) + ssig0(0x80000000u);
+    w[24] = padd(op, vs1(op, w[22]), w[17]) + 0x80000000u;
+    w[25] = padd(op, vs1(op, w[23]), w[18]);
+    w[26] = padd(op, vs1(op, w[24]), w[19]);
+    w[27] = padd(op, vs1(op, w[25]), w[20]);
+    w[28] = padd(op, vs1(op, w[26]), w[21]);
+    w[29] = padd(op, vs1(op, w[27]), w[22]);
+    w[30] = padd(op, vs1(op, w[28]), w[23]) + ssig0(0x100u);
+    w[31] = padd(op, padd(op, vs1(op, w[29]), w[24]), vs0(op, w[16])) + 0x100u;
 #pragma unroll
     for (int i = 32; i < 61; i++) w[i] = sched(op, w[i - 2], w[i - 7], w[i - 15], w[i - 16]);
 
@@ -514,15 +530,15 @@ OTD_HD vw<V> scan_core_compact(const JobConsts& jc, const vw<V>& w3, const Ops<K
             a = w3 + jc.ca3;      b = bc<V>(jc.a3); c = bc<V>(jc.b3); d = bc<V>(jc.c3);
             e = w3 + jc.ce3;      f = bc<V>(jc.e3); g = bc<V>(jc.f3); h = bc<V>(jc.g3);
             {
-                vw<V> t1 = vS1(op, e) + ch(e, f, g) + jc.k4;                  // round 4
-                vw<V> e5 = t1 + jc.c3;
-                vw<V> a5 = t1 + vS0(op, a) + maj(a, b, c);
-                t1 = vS1(op, e5) + ch(e5, e, f) + jc.k5;                      // round 5
-                vw<V> e6 = t1 + jc.b3;
-                vw<V> a6 = t1 + vS0(op, a5) + maj(a5, a, b);
-                t1 = vS1(op, e6) + ch(e6, e5, e) + jc.k6;                     // round 6
-                vw<V> e7 = t1 + jc.a3;
-                vw<V> a7 = t1 + vS0(op, a6) + maj(a6, a5, a);
+                vw<V> t1 = cadd(op, padd(op, vS1(op, e), ch(e, f, g)), jc.k4);                  // round 4
+                vw<V> e5 = cadd(op, t1, jc.c3);
+                vw<V> a5 = padd(op, padd(op, t1, vS0(op, a)), maj(a, b, c));
+                t1 = cadd(op, padd(op, vS1(op, e5), ch(e5, e, f)), jc.k5);                      // round 5
+                vw<V> e6 = cadd(op, t1, jc.b3);
+                vw<V> a6 = padd(op, padd(op, t1, vS0(op, a5)), maj(a5, a, b));
+                t1 = cadd(op, padd(op, vS1(op, e6), ch(e6, e5, e)), jc.k6);                     // round 6
+                vw<V> e7 = cadd(op, t1, jc.a3);
+                vw<V> a7 = padd(op, padd(op, t1, vS0(op, a6)), maj(a6, a5, a));
                 vw<V> a4 = a, e4 = e;
                 a = a7; b = a6; c = a5; d = a4; e = e7; f = e6; g = e5; h = e4;
             }
@@ -542,13 +558,13 @@ OTD_HD vw<V> scan_core_compact(const JobConsts& jc, const vw<V>& w3, const Ops<K
             x[22] = vs1(op, x[20]) + 0x280u;
             x[23] = vs1(op, x[21]) + jc.w16;
             x[24] = vs1(op, x[22]) + jc.w17;
-            x[25] = vs1(op, x[23]) + x[18];
-            x[26] = vs1(op, x[24]) + x[19];
-            x[27] = vs1(op, x[25]) + x[20];
-            x[28] = vs1(op, x[26]) + x[21];
-            x[29] = vs1(op, x[27]) + x[22];
-            x[30] = vs1(op, x[28]) + x[23] + ssig0(0x280u);
-            x[31] = vs1(op, x[29]) + x[24] + jc.c31;
+            x[25] = padd(op, vs1(op, x[23]), x[18]);
+            x[26] = padd(op, vs1(op, x[24]), x[19]);
+            x[27] = padd(op, vs1(op, x[25]), x[20]);
+            x[28] = padd(op, vs1(op, x[26]), x[21]);
+            x[29] = padd(op, vs1(op, x[27]), x[22]);
+            x[30] = padd(op, vs1(op, x[28]), x[23]) + ssig0(0x280u);
+            x[31] = padd(op, vs1(op, x[29]), x[24]) + jc.c31;
             rnd(op, h, a, b, c, d, e, f, g, jc.kw16);
             rnd(op, g, h, a, b, c, d, e, f, jc.kw17);
             rnd(op, f, g, h, a, b, c, d, e, x[18], Kc(18));
@@ -578,22 +594,22 @@ OTD_HD vw<V> scan_core_compact(const JobConsts& jc, const vw<V>& w3, const Ops<K
             vw<V> x[32];
             x[0] = a + jc.mid[0]; x[1] = b + jc.mid[1]; x[2] = c + jc.mid[2]; x[3] = d + jc.mid[3];
             x[4] = e + jc.mid[4]; x[5] = f + jc.mid[5]; x[6] = g + jc.mid[6]; x[7] = h + jc.mid[7];
-            x[16] = vs0(op, x[1]) + x[0];
-            x[17] = vs0(op, x[2]) + x[1] + ssig1(0x100u);
-            x[18] = vs1(op, x[16]) + vs0(op, x[3]) + x[2];
-            x[19] = vs1(op, x[17]) + vs0(op, x[4]) + x[3];
-            x[20] = vs1(op, x[18]) + vs0(op, x[5]) + x[4];
-            x[21] = vs1(op, x[19]) + vs0(op, x[6]) + x[5];
+            x[16] = padd(op, vs0(op, x[1]), x[0]);
+            x[17] = padd(op, vs0(op, x[2]), x[1]) + ssig1(0x100u);
+            x[18] = padd(op, padd(op, vs1(op, x[16]), vs0(op, x[3])), x[2]);
+            x[19] = padd(op, padd(op, vs1(op, x[17]), vs0(op, x[4])), x[3]);
+            x[20] = padd(op, padd(op, vs1(op, x[18]), vs0(op, x[5])), x[4]);
+            x[21] = padd(op, padd(op, vs1(op, x[19]), vs0(op, x[6])), x[5]);
             x[22] = sched(op, x[20], bc<V>(0x100u), x[7], x[6]);
-            x[23] = vs1(op, x[21]) + x[16] + x[7] + ssig0(0x80000000u);
-            x[24] = vs1(op, x[22]) + x[17] + 0x80000000u;
-            x[25] = vs1(op, x[23]) + x[18];
-            x[26] = vs1(op, x[24]) + x[19];
-            x[27] = vs1(op, x[25]) + x[20];
-            x[28] = vs1(op, x[26]) + x[21];
-            x[29] = vs1(op, x[27]) + x[22];
-            x[30] = vs1(op, x[28]) + x[23] + ssig0(0x100u);
-            x[31] = vs1(op, x[29]) + x[24] + vs0(op, x[16]) + 0x100u;
+            x[23] = padd(op, padd(op, vs1(op, x[21]), x[16]), x[7]) + ssig0(0x80000000u);
+            x[24] = padd(op, vs1(op, x[22]), x[17]) + 0x80000000u;
+            x[25] = padd(op, vs1(op, x[23]), x[18]);
+            x[26] = padd(op, vs1(op, x[24]), x[19]);
+            x[27] = padd(op, vs1(op, x[25]), x[20]);
+            x[28] = padd(op, vs1(op, x[26]), x[21]);
+            x[29] = padd(op, vs1(op, x[27]), x[22]);
+            x[30] = padd(op, vs1(op, x[28]), x[23]) + ssig0(0x100u);
+            x[31] = padd(op, padd(op, vs1(op, x[29]), x[24]), vs0(op, x[16])) + 0x100u;
             a = bc<V>(IV0); b = bc<V>(IV1); c = bc<V>(IV2); d = bc<V>(IV3);
             e = bc<V>(IV4); f = bc<V>(IV5); g = bc<V>(IV6); h = bc<V>(IV7);
             {
