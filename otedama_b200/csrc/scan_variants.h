@@ -19,7 +19,7 @@ struct RingEntry;
 // them unless the environment says OTD_ALLOW_EXPERIMENTAL=1.
 //
 // Measured on B200 (profiles/r1_variant_sweep.log), GH/s per GPU over a full 2^32 scan:
-//   add_sp_b5 9.31 | add_t1x_b5 9.24 | c_add_sp_b4 ~9.0 | alu_b5 8.25 | c_alu_b4 8.16
+//   add_sp_b5 9.32 | add_t1x_b5 9.25 | c_add_t1x_b4 9.0-9.1 | alu_b5 8.25 | c_alu_b4 8.16
 #define OTD_KN_ADD1 (otd::KN_E | otd::KN_W1)               /* 2-input adds: one IMAD replaces one ALU add */
 #define OTD_KN_ADDS (OTD_KN_ADD1 | otd::KN_A | otd::KN_W2) /* every immediate-free add except t1's */
 #define OTD_KN_T1X (OTD_KN_ADDS | otd::KN_T1X)             /* ... plus t1 split without an immediate IMAD */
@@ -28,7 +28,7 @@ struct RingEntry;
     X(0, "add_sp_b5", 1, 16, OTD_KN_BEST, false, 5)                                                 \
     X(1, "add_t1x_b5", 1, 16, OTD_KN_T1X, false, 5)                                                 \
     X(2, "alu_b5", 1, 16, 0u, false, 5)                                                             \
-    X(3, "c_add_sp_b4", 1, 16, otd::KN_COMPACT | OTD_KN_BEST, false, 4)                             \
+    X(3, "c_add_t1x_b4", 1, 16, otd::KN_COMPACT | OTD_KN_T1X, false, 4)                           \
     X(4, "c_alu_b4", 1, 16, otd::KN_COMPACT, false, 4)                                              \
     X(5, "add_sp_v2_b2", 2, 8, OTD_KN_BEST, false, 2)                                               \
     X(6, "h_alu", 1, 16, 0u, true, 5)                                                               \
