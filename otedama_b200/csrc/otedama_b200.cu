@@ -520,9 +520,10 @@ struct ScanVariant {
     int v, iter;
     unsigned knobs;
     bool half;  // experiment: stops after hash 1, does not compute SHA-256d
+    int block;  // threads per block
     otd_scan_launch_fn fn;
 };
-#define OTD_TABLE_ROW(idx, name, v, iter, kn, half, minb) {name, v, iter, kn, half, otd_scan_launch_##idx},
+#define OTD_TABLE_ROW(idx, name, v, iter, kn, half, minb, block) {name, v, iter, kn, half, block, otd_scan_launch_##idx},
 static const ScanVariant kAllVariants[] = {OTD_SCAN_VARIANTS(OTD_TABLE_ROW)};
 #undef OTD_TABLE_ROW
 static const int kNumAllVariants = (int)(sizeof kAllVariants / sizeof kAllVariants[0]);
@@ -892,7 +893,7 @@ class Engine {
                     CU_TRY(cudaEventRecord(s.edone, stream));
                     s.busy = true;
                     s.count = cnt;
-                    s.tile = (uint64_t)kScanBlock * kv.v * kv.iter;
+                    s.tile = (uint64_t)kv.block * kv.v * kv.iter;
                     s.en2 = wc.has_coinbase ? en2 : 0;
                     s.version = h_versions[i];
                 }

@@ -68,8 +68,8 @@ __device__ __forceinline__ void ring_push_warp(bool hit, uint32_t nonce, uint32_
 // V: candidates interleaved per thread; ITER: sequential batches per thread;
 // KN: instruction-placement knobs (scan_core.cuh).
 // MINB: minimum resident blocks per SM handed to __launch_bounds__ (register budget = 65536 / (256*MINB)).
-template <int V, int ITER, unsigned KN, bool HALF = false, int MINB = 1>
-__global__ void __launch_bounds__(kScanBlock, MINB)
+template <int V, int ITER, unsigned KN, bool HALF = false, int MINB = 1, int BLOCK = kScanBlock>
+__global__ void __launch_bounds__(BLOCK, MINB)
 scan_kernel(const __grid_constant__ JobConsts jc, const __grid_constant__ PipeMults pm,
             uint32_t nonce_begin, unsigned long long count,
             uint32_t instance, RingHeader* ring, RingEntry* entries, uint32_t cap,
@@ -79,16 +79,16 @@ scan_kernel(const __grid_constant__ JobConsts jc, const __grid_constant__ PipeMu
     if (*reinterpret_cast<const volatile unsigned int*>(stop_gen) != my_gen) return;
 
     const Ops<KN> op{pm};
-    constexpr unsigned long long kTile = (unsigned long long)kScanBlock * V * ITER;
+    constexpr unsigned long long kTile = (unsigned long long)BLOCK * V * ITER;
     const unsigned long long tile0 = (unsigned long long)blockIdx.x * kTile + threadIdx.x;
 
 #pragma unroll 1
     for (int it = 0; it < ITER; it++) {
-        const unsigned long long idx0 = tile0 + (unsigned long long)it * (kScanBlock * V);
+        const unsigned long long idx0 = tile0 + (unsigned long long)it * (BLOCK * V);
         vw<V> w3;
 #pragma unroll
         for (int v = 0; v < V; v++)
-            w3.x[v] = __byte_perm(nonce_begin + (uint32_t)idx0 + (uint32_t)(v * kScanBlock), 0, 0x0123);
+            w3.x[v] = __byte_perm(nonce_begin + (uint32_t)idx0 + (uint32_t)(v * BLOCK), 0, 0x0123);
         const vw<V> e60 = (KN & KN_COMPACT) ? scan_core_compact<V, KN>(jc, w3, op) : scan_core<V, KN, HALF>(jc, w3, op);
 
         unsigned cmask = 0;
@@ -101,7 +101,7 @@ scan_kernel(const __grid_constant__ JobConsts jc, const __grid_constant__ PipeMu
         if (__any_sync(0xffffffffu, cmask != 0)) {  // rare, warp-uniform
 #pragma unroll 1
             for (int v = 0; v < V; v++) {
-                const unsigned long long idx = idx0 + (unsigned long long)v * kScanBlock;
+                const unsigned long long idx = idx0 + (unsigned long long)v * BLOCK;
                 const uint32_t nonce = nonce_begin + (uint32_t)idx;
                 uint32_t dig[8];
                 bool hit = false;

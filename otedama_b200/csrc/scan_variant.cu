@@ -8,15 +8,15 @@
 #endif
 
 namespace {
-template <int V, int ITER, unsigned KN, bool HALF, int MINB>
+template <int V, int ITER, unsigned KN, bool HALF, int MINB, int BLOCK>
 cudaError_t launch(const otd::JobConsts& jc, uint32_t nonce_begin, unsigned long long count, uint32_t instance,
                    otd::RingHeader* hdr, otd::RingEntry* ent, uint32_t cap, const unsigned int* stop,
                    unsigned int gen, cudaStream_t st)
 {
-    constexpr unsigned long long tile = (unsigned long long)otd::kScanBlock * V * ITER;
+    constexpr unsigned long long tile = (unsigned long long)BLOCK * V * ITER;
     const unsigned grid = (unsigned)((count + tile - 1) / tile);
     if (grid == 0) return cudaSuccess;
-    otd::scan_kernel<V, ITER, KN, HALF, MINB><<<grid, otd::kScanBlock, 0, st>>>(jc, otd::make_pipe_mults(), nonce_begin, count,
+    otd::scan_kernel<V, ITER, KN, HALF, MINB, BLOCK><<<grid, BLOCK, 0, st>>>(jc, otd::make_pipe_mults(), nonce_begin, count,
                                                                       instance, hdr, ent, cap, stop, gen);
     return cudaGetLastError();
 }
@@ -29,14 +29,15 @@ struct Sel {
     unsigned kn;
     bool half;
     int minb;
+    int block;
 };
 constexpr Sel select(int want)
 {
-#define OTD_PICK(idx, name, v, iter, kn, half, minb) \
-    if (want == idx) return Sel{v, iter, kn, half, minb};
+#define OTD_PICK(idx, name, v, iter, kn, half, minb, block) \
+    if (want == idx) return Sel{v, iter, kn, half, minb, block};
     OTD_SCAN_VARIANTS(OTD_PICK)
 #undef OTD_PICK
-    return Sel{1, 16, 0u, false, 1};
+    return Sel{1, 16, 0u, false, 1, 256};
 }
 constexpr Sel kSel = select(OTD_VIDX);
 }  // namespace
@@ -48,5 +49,5 @@ cudaError_t OTD_FN_NAME(OTD_VIDX)(const otd::JobConsts& jc, uint32_t nonce_begin
                                   uint32_t instance, otd::RingHeader* hdr, otd::RingEntry* ent, uint32_t cap,
                                   const unsigned int* stop, unsigned int gen, cudaStream_t st)
 {
-    return launch<kSel.v, kSel.iter, kSel.kn, kSel.half, kSel.minb>(jc, nonce_begin, count, instance, hdr, ent, cap, stop, gen, st);
+    return launch<kSel.v, kSel.iter, kSel.kn, kSel.half, kSel.minb, kSel.block>(jc, nonce_begin, count, instance, hdr, ent, cap, stop, gen, st);
 }

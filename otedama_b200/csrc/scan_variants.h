@@ -13,26 +13,27 @@ struct RingHeader;
 struct RingEntry;
 }  // namespace otd
 
-// index, name, V, ITER, knobs, HALF, MINB.  Production variants first (indices below
+// index, name, V, ITER, knobs, HALF, MINB, BLOCK.  Production variants first (indices below
 // OTD_NUM_PRODUCTION_VARIANTS); the rest are performance experiments: "h_*" variants
 // stop after hash 1 (HALF) and do NOT compute SHA-256d — the library refuses to run
 // them unless the environment says OTD_ALLOW_EXPERIMENTAL=1.
 //
 // Measured on B200 (profiles/r1_variant_sweep.log), GH/s per GPU over a full 2^32 scan:
 //   add_sp_b5 9.32 | add_t1x_b5 9.25 | c_add_t1x_b4 9.0-9.1 | alu_b5 8.25 | c_alu_b4 8.16
+// Block shape at the same 40 warps/SM: 256 = 512 threads (9.32) > 1024 (9.26) > 128 (8.68); ITER 8..64: no effect.
 #define OTD_KN_ADD1 (otd::KN_E | otd::KN_W1)               /* 2-input adds: one IMAD replaces one ALU add */
 #define OTD_KN_ADDS (OTD_KN_ADD1 | otd::KN_A | otd::KN_W2) /* every immediate-free add except t1's */
 #define OTD_KN_T1X (OTD_KN_ADDS | otd::KN_T1X)             /* ... plus t1 split without an immediate IMAD */
 #define OTD_KN_BEST (OTD_KN_T1X | otd::KN_SP)              /* ... plus the reg+reg adds of the specialised parts */
 #define OTD_SCAN_VARIANTS(X)                                                                        \
-    X(0, "add_sp_b5", 1, 16, OTD_KN_BEST, false, 5)                                                 \
-    X(1, "add_t1x_b5", 1, 16, OTD_KN_T1X, false, 5)                                                 \
-    X(2, "alu_b5", 1, 16, 0u, false, 5)                                                             \
-    X(3, "c_add_t1x_b4", 1, 16, otd::KN_COMPACT | OTD_KN_T1X, false, 4)                           \
-    X(4, "c_alu_b4", 1, 16, otd::KN_COMPACT, false, 4)                                              \
-    X(5, "add_sp_v2_b2", 2, 8, OTD_KN_BEST, false, 2)                                               \
-    X(6, "h_alu", 1, 16, 0u, true, 5)                                                               \
-    X(7, "h_add_sp", 1, 16, OTD_KN_BEST, true, 5)
+    X(0, "add_sp_b5", 1, 16, OTD_KN_BEST, false, 5, 256)                                                 \
+    X(1, "add_t1x_b5", 1, 16, OTD_KN_T1X, false, 5, 256)                                                 \
+    X(2, "alu_b5", 1, 16, 0u, false, 5, 256)                                                             \
+    X(3, "c_add_t1x_b4", 1, 16, otd::KN_COMPACT | OTD_KN_T1X, false, 4, 256)                           \
+    X(4, "c_alu_b4", 1, 16, otd::KN_COMPACT, false, 4, 256)                                              \
+    X(5, "add_sp_v2_b2", 2, 8, OTD_KN_BEST, false, 2, 256)                                               \
+    X(6, "h_alu", 1, 16, 0u, true, 5, 256)                                                          \
+    X(7, "h_add_sp", 1, 16, OTD_KN_BEST, true, 5, 256)
 
 #define OTD_NUM_PRODUCTION_VARIANTS 6
 #define OTD_DEFAULT_VARIANT 0
@@ -42,7 +43,7 @@ typedef cudaError_t (*otd_scan_launch_fn)(const otd::JobConsts&, uint32_t nonce_
                                           otd::RingHeader*, otd::RingEntry*, uint32_t cap,
                                           const unsigned int* stop, unsigned int gen, cudaStream_t);
 
-#define OTD_DECLARE_VARIANT(idx, name, v, iter, kn, half, minb)                                                   \
+#define OTD_DECLARE_VARIANT(idx, name, v, iter, kn, half, minb, block)                                                   \
     cudaError_t otd_scan_launch_##idx(const otd::JobConsts&, uint32_t, unsigned long long, uint32_t, \
                                       otd::RingHeader*, otd::RingEntry*, uint32_t, const unsigned int*, \
                                       unsigned int, cudaStream_t);

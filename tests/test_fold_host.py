@@ -45,7 +45,7 @@ def test_every_production_variant_policy_is_host_checked():
     import re
     txt = open(os.path.join(HERE, "..", "otedama_b200", "csrc", "scan_variants.h")).read()
     nprod = int(re.search(r"#define OTD_NUM_PRODUCTION_VARIANTS (\d+)", txt).group(1))
-    rows = re.findall(r"X\((\d+), \"(\w+)\", (\d+), (\d+), ([^,]+?), (true|false), \d+\)", txt)
+    rows = re.findall(r"X\((\d+), \"(\w+)\", (\d+), (\d+), ([^,]+?), (true|false), \d+, \d+\)", txt)
     assert len(rows) >= nprod
     env = {"OTD_KN_ADD1": ADD1, "OTD_KN_ADDS": ADDS, "OTD_KN_T1X": ADDS | KN["T1X"], "OTD_KN_BEST": ADDS | KN["T1X"] | KN["SP"], **{f"otd::KN_{k}": v for k, v in KN.items()}}
     for idx, name, v, it, kn, half in rows[:nprod]:
