@@ -176,3 +176,12 @@ def test_hash_rate_string(product):
     for hps, want in ((500, "500 H/s"), (1500, "1.50 kH/s"), (2.5e6, "2.50 MH/s"), (3.7e9, "3.70 GH/s"),
                       (120e12, "120.00 TH/s")):
         assert miner.hash_rate_string(hps) == want
+
+
+def test_missing_library_fails_loudly(product, monkeypatch):
+    """No silent fallback: if libotedama_b200.so is not there, loading raises."""
+    from otedama_b200 import capi
+    monkeypatch.setattr(capi, "_lib", None)
+    monkeypatch.setattr(capi, "LIB_PATH", "/nonexistent/libotedama_b200.so")
+    with pytest.raises(capi.OtdError, match="no CPU fallback"):
+        capi.lib()
