@@ -421,6 +421,42 @@ def test_worker_set_work_aborts_a_long_launch_quickly(miner):
         assert dt < 0.25, f"job switch took {dt:.3f}s"   # a full 2^32 launch would take ~0.4 s
 
 
+def test_worker_survives_rapid_job_switching(miner, oracle):
+    """Host-runtime stress: 150 set_work calls (new job / pause / resume) at random moments of
+    the launches in flight.  No hang, no stale-job confusion: every share carries the job id
+    and work_seq of a job that was actually set, and re-hashes correctly on the CPU."""
+    rnd = random.Random(123)
+    t = (1 << 238).to_bytes(32, "little")      # ~2^-18 of hashes
+    jobs = {}
+    with miner.Worker(miner.WorkerConfig(launch_log2=22)) as w:
+        shares = []
+        for k in range(150):
+            r = rnd.random()
+            if r < 0.2:
+                seq = w.set_work(None)
+            else:
+                i = rnd.randrange(1, 200)
+                f = W.config2_fields(i)
+                seq = w.set_work(miner.Work(job_id=1000 + k, header=mheader(miner, f), target=t, repeat=rnd.random() < 0.5,
+                                            nonce_begin=rnd.randrange(0, 1 << 31), nonce_count=1 << rnd.randrange(16, 26)))
+                jobs[seq] = (1000 + k, i)
+            time.sleep(rnd.choice([0, 0, 0.001, 0.004, 0.015]))
+            shares += w.poll_shares(256, 0)
+        w.set_work(None)
+        time.sleep(0.05)
+        shares += w.poll_shares(4096, 0)
+        st = w.stats()
+    assert st.hashes_total > 0 and st.shares_dropped == 0
+    assert len(shares) > 50
+    for s in shares:
+        assert s.work_seq in jobs and jobs[s.work_seq][0] == s.job_id
+    for s in rnd.sample(shares, 40):
+        f = W.config2_fields(jobs[s.work_seq][1])
+        oh = oheader(oracle, f)
+        oh.nonce = s.nonce
+        assert oracle.hash_header(oh) == s.hash and oracle.less_or_equal(s.hash, t)
+
+
 def test_worker_queue_overflow_counts_drops(miner):
     """Non-blocking send with a drop counter (worker.go:271-275)."""
     with miner.Worker(miner.WorkerConfig(queue_capacity=100, launch_log2=16)) as w:
