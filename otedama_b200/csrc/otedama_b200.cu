@@ -859,6 +859,11 @@ class Engine {
         CU_TRY(cudaSetDevice(dev));
         int rc = upload_blob(wc);
         if (rc) return rc;
+        // A previous run's abort write travels on `aux`: make sure it has landed before this run's
+        // generation is written, or it could overwrite it and make every block of this run exit.
+        CU_TRY(cudaStreamSynchronize(aux));
+        CU_TRY(cudaStreamSynchronize(stream));
+        for (auto& s : slot) s.busy = false;  // nothing of an earlier (possibly failed) run is in flight now
         gen += 1;
         if (gen == 0) gen = 1;
         h_gen[0] = gen;
@@ -910,6 +915,7 @@ class Engine {
             CU_TRY(cudaEventElapsedTime(&span, ev_first, ev_last));
             rs.span_ms += span;
         }
+        if (abort_sent) CU_TRY(cudaStreamSynchronize(aux));
         return OTD_OK;
     }
 };
@@ -1007,6 +1013,7 @@ extern "C" int otd_scan_headers(int device_index, const otd_header_t* headers, u
     }
     CU_TRY(cudaSetDevice(device_index));
     Slot& s = eng->slot[0];
+    CU_TRY(cudaStreamSynchronize(eng->aux));
     eng->gen += 1;
     if (eng->gen == 0) eng->gen = 1;
     eng->h_gen[0] = eng->gen;
