@@ -147,3 +147,37 @@ def test_v1_notify_work_unit_scans_like_the_oracle(eng, oracle):
         want += [(e, s.nonce, s.hash) for s in sh]
     assert sorted((s.extranonce2, s.nonce, s.hash) for s in r.shares) == sorted(want) and len(want) > 10
     assert all(s.job_id == 12 and s.ntime == 0x60000000 and s.version == 0x20000000 for s in r.shares)
+
+
+@pytest.mark.gpu
+def test_block_170_is_found_from_its_notify_form(eng, oracle, golden):
+    """Real chain data end to end: block 170 expressed as a Stratum V1 notify (coinbase split around
+    its extranonce byte, one merkle branch) -> work unit -> K3/K2/K1 on the GPU must find exactly the
+    mined (extranonce2, nonce) with the published block hash."""
+    engine, miner = eng
+    b = golden["reference_vectors"]["real_world_anchors"]["block170"]
+    cb = bytes.fromhex(b["coinbase_tx_hex"])
+    k = b["stratum_split"]["coinb1_len"]
+    prev = bytes.fromhex(b["prev_hash_display"])[::-1]
+    prev_wire = b"".join(prev[4 * i:4 * i + 4][::-1] for i in range(8)).hex()
+    params = ["170", prev_wire, cb[:k].hex(), cb[k + 1:].hex(), [bytes.fromhex(b["second_txid_display"])[::-1].hex()],
+              "%08x" % b["version"], b["bits"], "%08x" % b["time"], True]
+    w = engine.work_from_v1_notify(params, "", 1, 1.0, extranonce2_begin=0, extranonce2_count=4)
+    w.nonce_begin, w.nonce_count = b["nonce"] - (1 << 20), 1 << 21
+    r = miner.scan(w)
+    assert [(s.extranonce2, s.nonce, s.hash[::-1].hex()) for s in r.shares] == [(2, b["nonce"], b["hash_display"])]
+    assert r.hashes == 4 << 21 and r.launches == 4
+    inst = miner.prepare_instances(w, 2, 1)[0]
+    assert inst.merkle_root[::-1].hex() == b["merkle_root_display"] and inst.extranonce2 == 2
+
+
+@pytest.mark.gpu
+def test_block_1_nonce_is_found(eng, golden):
+    engine, miner = eng
+    rw = golden["reference_vectors"]["real_world_anchors"]
+    h = miner.parse_header(bytes.fromhex(rw["block1_header_hex"]))
+    n = h.nonce
+    h.nonce = 0
+    r = miner.scan(miner.Work(header=h, nbits=h.bits, target=miner.target_from_nbits(h.bits), nonce_begin=n - 70000,
+                              nonce_count=140000))
+    assert [(s.nonce, s.hash[::-1].hex()) for s in r.shares] == [(n, rw["block1_hash_display"])]

@@ -191,3 +191,41 @@ def test_bip320_versions(oracle, golden):
     assert len(seen) == 302
     for k, want in golden["synthetic_windows"]["config4_versions_k"].items():
         assert oracle.bip320_version(v2["version"], v2["mask"], int(k)) == want
+
+
+def _rw(golden):
+    return golden["reference_vectors"]["real_world_anchors"]
+
+
+def test_real_world_anchors_pin_the_unpinned_subpaths(oracle, golden):
+    """Public chain data (verified with hashlib here, not trusted): block 1 (prev-hash = the
+    reference's genesis hash vector) and block 170 (coinbase -> txid -> merkle fold -> header)."""
+    rw = _rw(golden)
+    h1 = bytes.fromhex(rw["block1_header_hex"])
+    genesis_hash = golden["reference_vectors"]["sha256d"][0]["hash_hex"]
+    assert h1[4:36].hex() == genesis_hash                         # ties to the reference-pinned vector
+    assert oracle.sha256d(h1)[::-1].hex() == oracle.sha256d_hashlib(h1)[::-1].hex() == rw["block1_hash_display"]
+    assert oracle.Header.parse(h1).nonce == rw["block1_nonce"]
+    b = rw["block170"]
+    cb = bytes.fromhex(b["coinbase_tx_hex"])
+    assert oracle.sha256d_hashlib(cb)[::-1].hex() == b["coinbase_txid_display"]
+    sp = b["stratum_split"]
+    k = sp["coinb1_len"]
+    en2 = oracle.extranonce2_bytes(sp["extranonce2_value"], sp["extranonce2_size"])
+    assert cb[k:k + 1] == en2
+    branch = [bytes.fromhex(b["second_txid_display"])[::-1]]
+    root = oracle.v1_merkle_root(cb[:k], b"", en2, cb[k + 1:], branch)
+    assert root[::-1].hex() == b["merkle_root_display"]
+    assert oracle.v1_merkle_root(cb[:k], b"", en2, cb[k + 1:], []) [::-1].hex() == b["coinbase_txid_display"]
+    hdr = oracle.Header(b["version"], bytes.fromhex(b["prev_hash_display"])[::-1], root, b["time"],
+                        int(b["bits"], 16), b["nonce"])
+    hh = oracle.hash_header(hdr)
+    assert hh[::-1].hex() == b["hash_display"]
+    assert oracle.meets_target(hh, int(b["bits"], 16))
+    # the same through the notify form (prev-hash words swapped, big-endian hex scalars)
+    prev_wire = b"".join(hdr.prev_hash[4 * i:4 * i + 4][::-1] for i in range(8)).hex()
+    params = ["170", prev_wire, cb[:k].hex(), cb[k + 1:].hex(), [branch[0].hex()], "%08x" % b["version"], b["bits"],
+              "%08x" % b["time"], True]
+    oh = oracle.v1_header(params, b"", en2)
+    oh.nonce = b["nonce"]
+    assert oracle.hash_header(oh)[::-1].hex() == b["hash_display"]
