@@ -16,7 +16,9 @@ Two layers:
 
 Parity: pinned by the reference's own vectors (see tests/test_oracle.py and
 tests/golden/reference_vectors.json); the V1-coinbase and BIP-320 helpers are
-"parity unpinned" (no reference code or test exists for them).
+"parity unpinned" (no reference code or test exists for them) — the V1 ones are
+anchored to public chain data instead (block 170 end to end, re-derived with
+hashlib in the tests).
 """
 from __future__ import annotations
 

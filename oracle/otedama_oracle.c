@@ -22,7 +22,10 @@
  *
  * UNPINNED sub-paths (the reference has neither code nor tests for them; they
  * follow the public Stratum V1 / BIP-320 conventions):
- *   orc_v1_merkle_root, orc_v1_header, orc_bip320_version.
+ *   orc_v1_merkle_root, orc_extranonce2_bytes, orc_bip320_version.
+ * orc_v1_merkle_root is additionally anchored to public chain data that the
+ * tests re-derive with hashlib (genesis coinbase -> genesis merkle root; block
+ * 170: coinbase -> txid -> merkle fold -> header -> published block hash).
  *
  * Two compression back-ends are provided because Go's crypto/sha256
  * dispatches to SHA-NI on amd64 when the CPU has it: a portable scalar
