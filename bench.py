@@ -275,7 +275,7 @@ def main():
         #    (IMAD.WIDE does not co-issue) against the same ALU-pipe rate -> the real ceiling.
         alu_only_ops = 1804
         roofline = {"bound": "int-issue", "achieved": achieved / 1e12, "peak": peak_alu / 1e12,
-                    "unit": "Tint-op/s", "frac": achieved / peak_alu, "traffic": 89344,
+                    "unit": "Tint-op/s", "frac": achieved / peak_alu, "traffic": 94464,
                     "note": ("achieved = per-GPU H/s x 2450 algorithmic 3-input integer ops/hash (SURVEY §8d); "
                              "peak = ALU-pipe rate (SHF/LOP3/IADD3 at the SHA mix) measured on this GPU in this run, "
                              "of measured; frac exceeds 1 because the kernel issues the ~650 adds/hash as IMAD on the "
@@ -284,8 +284,8 @@ def main():
                              "(profiles/r1_ncu_scan_kernel.csv): effectively none"),
                     "frac_two_pipe": per_gpu_hps * alu_only_ops / peak_alu,
                     "two_pipe_note": ("H/s x 1804 ALU-only ops/hash (SHF 1176 + LOP3 628) / measured ALU-pipe rate: "
-                                      "the ceiling once every add runs on the FMA pipe; ncu shows the ALU pipe 97.3% busy "
-                                      "with 1956 ALU-pipe instructions per hash"),
+                                      "the ceiling once every add runs on the FMA pipe; ncu shows the ALU pipe 97.1% busy "
+                                      "with 1940 ALU-pipe instructions per hash"),
                     "peak_dual_issue": peak_dual / 1e12, "alg_ops_per_hash": ALG_OPS_PER_HASH,
                     "roofline_ghs_per_gpu": peak_alu / ALG_OPS_PER_HASH / 1e9,
                     "two_pipe_roofline_ghs_per_gpu": peak_alu / alu_only_ops / 1e9}
