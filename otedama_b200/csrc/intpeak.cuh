@@ -26,7 +26,10 @@ enum IntPeakMode {
     IPM_ALU2_WIDE = 12,  // 1 SHF + 1 LOP3 : 1 IMAD.WIDE                 (both pipes)
     IPM_ALU2_FMA = 13,   // 1 SHF + 1 LOP3 : 1 IMAD                      (both pipes)
     IPM_ALU_WIDE_FMA = 14, // 2 ALU : 1 IMAD.WIDE : 1 IMAD               (the balanced SHA mix)
-    IPM_COUNT = 15
+    IPM_ALU2_FMA_IMM = 15,   // 1 SHF + 1 LOP3 : 1 IMAD with a 32-bit immediate addend
+    IPM_ALU2_FMA_CONST = 16, // 1 SHF + 1 LOP3 : 1 IMAD with a constant-bank (kernel parameter) addend
+    IPM_ALU2_FMA_PAIR = 17,  // 2 SHF + 2 LOP3 : 2 dependent IMADs back to back
+    IPM_COUNT = 18
 };
 
 #if defined(__CUDACC__)
@@ -39,7 +42,9 @@ __host__ __device__ constexpr int ip_ops_per_step(int mode)
 {
     return (mode == IPM_MIX_ALU || mode == IPM_MIX_DUAL || mode == IPM_MIX_DUAL1) ? 4
            : (mode == IPM_ALU_FMA || mode == IPM_ALU_WIDE)                        ? 2
-           : (mode == IPM_ALU2_WIDE || mode == IPM_ALU2_FMA)                      ? 3
+           : (mode == IPM_ALU2_WIDE || mode == IPM_ALU2_FMA || mode == IPM_ALU2_FMA_IMM ||
+              mode == IPM_ALU2_FMA_CONST)                                         ? 3
+           : (mode == IPM_ALU2_FMA_PAIR)                                          ? 6
            : (mode == IPM_ALU_WIDE_FMA)                                           ? 4
                                                                                   : 1;
 }
@@ -120,6 +125,21 @@ __global__ void __launch_bounds__(1024) int_peak_kernel(int iters, uint32_t one,
                     asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
                     asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
                     asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(z[c]));
+                } else if (MODE == IPM_ALU2_FMA_IMM) {
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("mad.lo.u32 %0, %0, %1, 0x5be0cd19;" : "+r"(y[c]) : "r"(one));
+                } else if (MODE == IPM_ALU2_FMA_CONST) {
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(seed));
+                } else if (MODE == IPM_ALU2_FMA_PAIR) {
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 11;" : "+r"(x[c]));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(z[c]));
+                    asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(x[c]));
                 } else if (MODE == IPM_ALU_WIDE_FMA) {
                     asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
                     asm volatile("{ .reg .u64 w;\n mul.wide.u32 w, %0, %2;\n mov.b64 {%0, %1}, w; }"
