@@ -95,7 +95,7 @@ extern "C" int otd_device_info(int idx, otd_device_info_t* out)
     CU_TRY(cudaGetDeviceProperties(&p, idx));
     memset(out, 0, sizeof *out);
     snprintf(out->id, sizeof out->id, "gpu-cuda%d", idx);
-    snprintf(out->model, sizeof out->model, "%s", p.name);
+    snprintf(out->model, sizeof out->model, "%.127s", p.name);
     snprintf(out->vendor, sizeof out->vendor, "nvidia");
     char bus[32] = {0};
     if (cudaDeviceGetPCIBusId(bus, sizeof bus, idx) == cudaSuccess) snprintf(out->pci_bus_id, sizeof out->pci_bus_id, "%s", bus);

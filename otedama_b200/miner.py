@@ -9,9 +9,8 @@ module is the Python harness bound to the same entry points.
 from __future__ import annotations
 
 import ctypes
-import time
 from dataclasses import dataclass, field
-from typing import Iterable, List, Optional, Sequence
+from typing import List, Optional, Sequence
 
 from . import capi
 from .capi import CHeader, CShare, CStats, CWork, CWorkerConfig, OtdError, check, lib
