@@ -89,6 +89,7 @@ template <int V> OTD_HD vw<V> maj(const vw<V>& a, const vw<V>& b, const vw<V>& c
 // selected shifts/rotations to IMAD.WIDE (x * 2^(32-n): hi = x>>n, lo = x<<(32-n))
 // so that both pipes fill.  The run-time multipliers live in the constant bank.
 // ---------------------------------------------------------------------------
+#define OTD_KN_Z_EIGHTHS(n) ((unsigned)(n) << 16)
 enum : unsigned {
     KN_E = 1u,       // e' = d + t1                 as IMAD
     KN_HKW = 2u,     // h + K + W                   as 2 IMAD instead of IADD3
@@ -104,12 +105,19 @@ enum : unsigned {
     KN_SP = 4096u,   // register+register adds of the specialised parts (first schedule words, rounds 4..6) as IMAD
                      // (adds with a constant-bank or immediate operand stay on the ALU: an IMAD with a
                      //  non-register addend raises dispatch stalls, measured with c[] operands as well)
+    KN_T1Z = 8192u,  // zero ALU adds in a round: t1 = IMAD(IMAD(h,1,IMAD(W,1v,K_imm)), 1, IMAD(Sigma1,1,Ch)); the
+                     // immediate-carrying IMAD uses a separate VECTOR-register 1 (one_v) so that all the other
+                     // IMADs keep their uniform-register 1 (an IMAD takes only one non-vector operand).
+                     // Applied to KN_Z_EIGHTHS(n)/8 of the rounds (the rest use the KN_T1X form): the best
+                     // FMA:ALU balance is an interior point (measured: 5/8..6/8).
+    KN_Z_SHIFT = 16u,  // bits 16..19: n of KN_Z_EIGHTHS(n), 1..8
     KN_COMPACT = 2048u,  // partially rolled body (scan_core_compact): the three fully generic 16-round blocks
                          // share one loop body so the code stays well inside the instruction cache
 };
 
 struct PipeMults {  // run-time constants the compiler cannot fold (kernel parameter)
     uint32_t one;                                  // 1
+    uint32_t zero;                                 // 0: threadIdx & zero makes one_v thread-variant for ptxas
     uint32_t m2, m13, m22, m6, m11, m25;           // 2^(32-n) for the Sigma rotations
     uint32_t m7, m18, m3, m17, m19, m10;           // ... and for sigma0 / sigma1
 };
@@ -117,6 +125,7 @@ OTD_HD PipeMults make_pipe_mults()
 {
     PipeMults m;
     m.one = 1u;
+    m.zero = 0u;
     m.m2 = 1u << 30; m.m13 = 1u << 19; m.m22 = 1u << 10; m.m6 = 1u << 26; m.m11 = 1u << 21; m.m25 = 1u << 7;
     m.m7 = 1u << 25; m.m18 = 1u << 14; m.m3 = 1u << 29; m.m17 = 1u << 15; m.m19 = 1u << 13; m.m10 = 1u << 22;
     return m;
@@ -148,6 +157,7 @@ OTD_HD void fma_wide(uint32_t x, uint32_t m, uint32_t& hi, uint32_t& lo)
 template <unsigned KN>
 struct Ops {
     PipeMults m;
+    uint32_t one_v = 1u;  // 1 in a vector register (KN_T1Z); set by the kernel
     OTD_HD uint32_t add_if(bool on_fma, uint32_t a, uint32_t b) const { return on_fma ? fma_add(a, b, m.one) : a + b; }
     OTD_HD uint32_t add3_if(bool on_fma, uint32_t a, uint32_t b, uint32_t c) const
     {
@@ -214,7 +224,13 @@ struct Ops {
     // t1 = h + Sigma1(e) + Ch(e,f,g) + K + W  (W a per-candidate word)
     OTD_HD uint32_t t1_kw(uint32_t h, uint32_t e, uint32_t f, uint32_t g, uint32_t w, uint32_t k) const
     {
-        if (KN & KN_T1X) {
+        if ((KN & KN_T1Z) && z_round(k)) {
+            const uint32_t kw = fma_add(w, k, one_v);
+            const uint32_t hk = fma_add(h, kw, m.one);
+            const uint32_t sc = fma_add(S1(e), ch(e, f, g), m.one);
+            return fma_add(hk, sc, m.one);
+        }
+        if (KN & (KN_T1X | KN_T1Z)) {
             const uint32_t x = fma_add(h, w, m.one);
             const uint32_t y = x + S1(e) + k;
             return fma_add(y, ch(e, f, g), m.one);
@@ -223,10 +239,22 @@ struct Ops {
         const uint32_t hk = add_if(KN & KN_HKW, h, kw);
         return add3_if(KN & KN_T1, hk, S1(e), ch(e, f, g));
     }
+    // KN_T1Z is applied to a fraction of the rounds, picked by three bits of the round constant (a fixed
+    // pseudo-random subset of the 64 constants): n eighths, n from the KN_Z_EIGHTHS field (0 reads as 8).
+    OTD_HD static constexpr unsigned z_eighths()
+    {
+        return ((KN >> KN_Z_SHIFT) & 15u) ? ((KN >> KN_Z_SHIFT) & 15u) : 8u;
+    }
+    OTD_HD static constexpr bool z_round(uint32_t k) { return ((k >> 7) & 7u) < z_eighths(); }
     // same with K + W a job constant or an immediate
     OTD_HD uint32_t t1_k(uint32_t h, uint32_t e, uint32_t f, uint32_t g, uint32_t k) const
     {
-        if (KN & KN_T1X) {
+        if ((KN & KN_T1Z) && z_round(k)) {
+            const uint32_t hk = fma_add(h, k, one_v);
+            const uint32_t sc = fma_add(S1(e), ch(e, f, g), m.one);
+            return fma_add(hk, sc, m.one);
+        }
+        if (KN & (KN_T1X | KN_T1Z)) {
             const uint32_t y = h + S1(e) + k;
             return fma_add(y, ch(e, f, g), m.one);
         }

@@ -78,7 +78,8 @@ scan_kernel(const __grid_constant__ JobConsts jc, const __grid_constant__ PipeMu
     // A newer job (or set_work(NULL)) bumps *stop_gen: blocks not yet started exit at once.
     if (*reinterpret_cast<const volatile unsigned int*>(stop_gen) != my_gen) return;
 
-    const Ops<KN> op{pm};
+    Ops<KN> op{pm};
+    if (KN & KN_T1Z) op.one_v = pm.one | (threadIdx.x & pm.zero);  // a 1 ptxas must keep in a vector register
     constexpr unsigned long long kTile = (unsigned long long)BLOCK * V * ITER;
     const unsigned long long tile0 = (unsigned long long)blockIdx.x * kTile + threadIdx.x;
 

@@ -19,21 +19,22 @@ struct RingEntry;
 // them unless the environment says OTD_ALLOW_EXPERIMENTAL=1.
 //
 // Measured on B200 (profiles/r1_variant_sweep.log), GH/s per GPU over a full 2^32 scan:
-//   add_sp_b5 9.32 | add_t1x_b5 9.25 | c_add_t1x_b4 9.0-9.1 | alu_b5 8.25 | c_alu_b4 8.16
-// Block shape at the same 40 warps/SM: 256 = 512 threads (9.32) > 1024 (9.26) > 128 (8.68); ITER 8..64: no effect.
+//   add_z6_b4 9.55 | add_sp_b5 9.32 | add_t1x_b5 9.25 | c_add_t1x_b4 9.0-9.1 | alu_b5 8.25 | c_alu_b4 8.16
+// Block shape at the same warps/SM: 256 = 512 threads > 1024 > 128; ITER 8..64: no effect.
 #define OTD_KN_ADD1 (otd::KN_E | otd::KN_W1)               /* 2-input adds: one IMAD replaces one ALU add */
 #define OTD_KN_ADDS (OTD_KN_ADD1 | otd::KN_A | otd::KN_W2) /* every immediate-free add except t1's */
 #define OTD_KN_T1X (OTD_KN_ADDS | otd::KN_T1X)             /* ... plus t1 split without an immediate IMAD */
-#define OTD_KN_BEST (OTD_KN_T1X | otd::KN_SP)              /* ... plus the reg+reg adds of the specialised parts */
+#define OTD_KN_SPX (OTD_KN_T1X | otd::KN_SP)               /* ... plus the reg+reg adds of the specialised parts */
+#define OTD_KN_BEST (OTD_KN_ADDS | otd::KN_SP | otd::KN_T1Z | OTD_KN_Z_EIGHTHS(6)) /* ... and no ALU add at all in 6/8 of the rounds */
 #define OTD_SCAN_VARIANTS(X)                                                                        \
-    X(0, "add_sp_b5", 1, 16, OTD_KN_BEST, false, 5, 256)                                                 \
-    X(1, "add_t1x_b5", 1, 16, OTD_KN_T1X, false, 5, 256)                                                 \
-    X(2, "alu_b5", 1, 16, 0u, false, 5, 256)                                                             \
-    X(3, "c_add_t1x_b4", 1, 16, otd::KN_COMPACT | OTD_KN_T1X, false, 4, 256)                           \
-    X(4, "c_alu_b4", 1, 16, otd::KN_COMPACT, false, 4, 256)                                              \
-    X(5, "add_sp_v2_b2", 2, 8, OTD_KN_BEST, false, 2, 256)                                               \
+    X(0, "add_z6_b4", 1, 16, OTD_KN_BEST, false, 4, 256)                                            \
+    X(1, "add_sp_b5", 1, 16, OTD_KN_SPX, false, 5, 256)                                             \
+    X(2, "alu_b5", 1, 16, 0u, false, 5, 256)                                                        \
+    X(3, "c_add_t1x_b4", 1, 16, otd::KN_COMPACT | OTD_KN_T1X, false, 4, 256)                        \
+    X(4, "c_alu_b4", 1, 16, otd::KN_COMPACT, false, 4, 256)                                         \
+    X(5, "add_z6_v2_b2", 2, 8, OTD_KN_BEST, false, 2, 256)                                          \
     X(6, "h_alu", 1, 16, 0u, true, 5, 256)                                                          \
-    X(7, "h_add_sp", 1, 16, OTD_KN_BEST, true, 5, 256)
+    X(7, "h_add_sp", 1, 16, OTD_KN_SPX, true, 5, 256)
 
 #define OTD_NUM_PRODUCTION_VARIANTS 6
 #define OTD_DEFAULT_VARIANT 0

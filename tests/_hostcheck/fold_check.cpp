@@ -62,6 +62,15 @@ int fc_scan_e60_kn(const uint8_t hdr76[76], const uint32_t* nonces, int v, unsig
         case KN_E | KN_W1 | KN_A | KN_W2: return run_v<KN_E | KN_W1 | KN_A | KN_W2>(jc, nonces, v, e60_out);
         case 2047: return run_v<2047>(jc, nonces, v, e60_out);
         case KN_COMPACT: return run_v<KN_COMPACT>(jc, nonces, v, e60_out);
+#define ZSET(n) (KN_E | KN_W1 | KN_A | KN_W2 | KN_SP | KN_T1Z | OTD_KN_Z_EIGHTHS(n))
+        case ZSET(1): return run_v<ZSET(1)>(jc, nonces, v, e60_out);
+        case ZSET(5): return run_v<ZSET(5)>(jc, nonces, v, e60_out);
+        case ZSET(6): return run_v<ZSET(6)>(jc, nonces, v, e60_out);
+        case ZSET(8): return run_v<ZSET(8)>(jc, nonces, v, e60_out);
+        case KN_COMPACT | ZSET(6): return run_v<KN_COMPACT | ZSET(6)>(jc, nonces, v, e60_out);
+        case ZSET(6) & ~KN_E: return run_v<ZSET(6) & ~KN_E>(jc, nonces, v, e60_out);
+        case ZSET(6) & ~KN_A: return run_v<ZSET(6) & ~KN_A>(jc, nonces, v, e60_out);
+        case ZSET(6) & ~KN_W2: return run_v<ZSET(6) & ~KN_W2>(jc, nonces, v, e60_out);
         case KN_E | KN_W1 | KN_A | KN_W2 | KN_T1X | KN_SP: return run_v<KN_E | KN_W1 | KN_A | KN_W2 | KN_T1X | KN_SP>(jc, nonces, v, e60_out);
         case KN_COMPACT | KN_E | KN_W1 | KN_A | KN_W2 | KN_T1X | KN_SP: return run_v<KN_COMPACT | KN_E | KN_W1 | KN_A | KN_W2 | KN_T1X | KN_SP>(jc, nonces, v, e60_out);
         case KN_COMPACT | KN_E | KN_W1 | KN_A | KN_W2 | KN_T1X: return run_v<KN_COMPACT | KN_E | KN_W1 | KN_A | KN_W2 | KN_T1X>(jc, nonces, v, e60_out);

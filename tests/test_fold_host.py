@@ -26,15 +26,22 @@ def fold():
     return L
 
 
-KN = dict(E=1, HKW=2, T1=4, A=8, W1=16, W2=32, SSHR=64, SROT=128, BS1=256, BS0=512, T1X=1024, COMPACT=2048, SP=4096)
+KN = dict(E=1, HKW=2, T1=4, A=8, W1=16, W2=32, SSHR=64, SROT=128, BS1=256, BS0=512, T1X=1024, COMPACT=2048, SP=4096, T1Z=8192)
 ADD1 = KN["E"] | KN["W1"]
 ADDS = ADD1 | KN["A"] | KN["W2"]
 CPT = KN["COMPACT"]
+
+
+def ZSET(n):
+    return ADDS | KN["SP"] | KN["T1Z"] | (n << 16)
+
+
 KNOB_SETS = [0, 1023, 63, ADDS, ADDS | KN["T1"], ADDS | KN["T1X"], ADD1 | KN["A"], ADD1 | KN["T1X"],
              ADD1 | KN["A"] | KN["T1X"], KN["T1"] | KN["A"] | KN["W2"], KN["E"] | KN["W1"] | KN["SSHR"],
              KN["E"] | KN["W1"] | KN["SSHR"] | KN["HKW"] | KN["BS1"],
              KN["E"] | KN["W1"] | KN["SSHR"] | KN["HKW"] | KN["BS1"] | KN["BS0"] | KN["SROT"],
-             ADDS | KN["T1X"] | KN["SP"], CPT | ADDS | KN["T1X"] | KN["SP"],
+             ADDS | KN["T1X"] | KN["SP"], CPT | ADDS | KN["T1X"] | KN["SP"], ZSET(1), ZSET(5), ZSET(6), ZSET(8), CPT | ZSET(6), ZSET(6) & ~KN["E"], ZSET(6) & ~KN["A"],
+             ZSET(6) & ~KN["W2"],
              CPT, CPT | ADDS | KN["T1X"], CPT | ADDS | KN["T1"], CPT | ADDS, CPT | ADD1 | KN["A"],
              CPT | 1023 | KN["T1X"]]
 
@@ -47,7 +54,7 @@ def test_every_production_variant_policy_is_host_checked():
     nprod = int(re.search(r"#define OTD_NUM_PRODUCTION_VARIANTS (\d+)", txt).group(1))
     rows = re.findall(r"X\((\d+), \"(\w+)\", (\d+), (\d+), ([^,]+?), (true|false), \d+, \d+\)", txt)
     assert len(rows) >= nprod
-    env = {"OTD_KN_ADD1": ADD1, "OTD_KN_ADDS": ADDS, "OTD_KN_T1X": ADDS | KN["T1X"], "OTD_KN_BEST": ADDS | KN["T1X"] | KN["SP"], **{f"otd::KN_{k}": v for k, v in KN.items()}}
+    env = {"OTD_KN_ADD1": ADD1, "OTD_KN_ADDS": ADDS, "OTD_KN_T1X": ADDS | KN["T1X"], "OTD_KN_SPX": ADDS | KN["T1X"] | KN["SP"], "OTD_KN_BEST": ZSET(6), **{f"otd::KN_{k}": v for k, v in KN.items()}}
     for idx, name, v, it, kn, half in rows[:nprod]:
         assert half == "false", f"production variant {name} must compute the full SHA-256d"
         val = 0
