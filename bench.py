@@ -275,17 +275,17 @@ def main():
         #    (IMAD.WIDE does not co-issue) against the same ALU-pipe rate -> the real ceiling.
         alu_only_ops = 1804
         roofline = {"bound": "int-issue", "achieved": achieved / 1e12, "peak": peak_alu / 1e12,
-                    "unit": "Tint-op/s", "frac": achieved / peak_alu, "traffic": 94464,
+                    "unit": "Tint-op/s", "frac": achieved / peak_alu, "traffic": 127488,
                     "note": ("achieved = per-GPU H/s x 2450 algorithmic 3-input integer ops/hash (SURVEY §8d); "
                              "peak = ALU-pipe rate (SHF/LOP3/IADD3 at the SHA mix) measured on this GPU in this run, "
-                             "of measured; frac exceeds 1 because the kernel issues the ~650 adds/hash as IMAD on the "
+                             "of measured; frac exceeds 1 because the kernel issues almost all of the ~650 adds/hash as IMAD on the "
                              "FMA pipe, which a one-pipe roofline does not model; traffic = dram__bytes_read+write "
                              "(bytes) of one 2^30-candidate launch from ncu --set full "
                              "(profiles/r1_ncu_scan_kernel.csv): effectively none"),
                     "frac_two_pipe": per_gpu_hps * alu_only_ops / peak_alu,
                     "two_pipe_note": ("H/s x 1804 ALU-only ops/hash (SHF 1176 + LOP3 628) / measured ALU-pipe rate: "
-                                      "the ceiling once every add runs on the FMA pipe; ncu shows the ALU pipe 97.1% busy "
-                                      "with 1940 ALU-pipe instructions per hash"),
+                                      "the ceiling once every add runs on the FMA pipe; ncu shows the ALU pipe 95.1% busy "
+                                      "with 1852 ALU-pipe instructions per hash"),
                     "peak_dual_issue": peak_dual / 1e12, "alg_ops_per_hash": ALG_OPS_PER_HASH,
                     "roofline_ghs_per_gpu": peak_alu / ALG_OPS_PER_HASH / 1e9,
                     "two_pipe_roofline_ghs_per_gpu": peak_alu / alu_only_ops / 1e9}
