@@ -82,12 +82,23 @@ template <int V> OTD_HD vw<V> maj(const vw<V>& a, const vw<V>& b, const vw<V>& c
 
 // ---------------------------------------------------------------------------
 // Instruction placement.  sm_100 issues integer work on two pipes (measured on
-// B200, see DESIGN.md): the ALU pipe (SHF/LOP3/IADD3/PRMT, 64 lanes/clk/SM) and
-// the FMA pipe (IMAD 64, IMAD.WIDE 60 lanes/clk/SM), ~119 lanes/clk/SM together.
-// A straight compile puts ~92% of SHA-256 on the ALU pipe and is bound by it;
-// the knobs below move selected adds to IMAD (x*1+y with a run-time 1) and
-// selected shifts/rotations to IMAD.WIDE (x * 2^(32-n): hi = x>>n, lo = x<<(32-n))
-// so that both pipes fill.  The run-time multipliers live in the constant bank.
+// B200, DESIGN.md §3.2): the ALU pipe (SHF/LOP3/IADD3/PRMT, 64 lanes/clk/SM) and
+// the FMA pipe (IMAD 64 lanes/clk/SM), ~119 lanes/clk/SM together.  A straight
+// compile puts ~92% of SHA-256 on the ALU pipe and is bound by it.  The knobs
+// below move work to the FMA pipe; what survived measurement:
+//   * adds as IMAD x*1+y — with the 1 in a UNIFORM register (two vector-register
+//     reads per IMAD; with the 1 in a vector register the register file cannot feed
+//     both pipes and the kernel loses 11 %).  An IMAD takes only one non-vector
+//     operand, so an IMAD that also carries an immediate needs a second, vector-
+//     register 1 (one_v) of its own — otherwise ptxas moves THE 1 into a vector
+//     register for every IMAD of the kernel;
+//   * shipped policy (OTD_KN_BEST): E | A | W1 | W2 | SP everywhere, and T1Z (no ALU
+//     add at all in the round) in 6/8 of the rounds, T1X (one IADD3 carrying the
+//     immediate round constant) in the rest.
+// Measured dead ends, kept so profiles/r1_variant_sweep.log stays reproducible:
+// rotations/shifts through IMAD.WIDE (SSHR/SROT/BS1/BS0: IMAD.WIDE does not
+// co-issue with ALU work), HKW and T1 (dependent IMAD chains with the 1 forced
+// into a vector register).
 // ---------------------------------------------------------------------------
 #define OTD_KN_Z_EIGHTHS(n) ((unsigned)(n) << 16)
 enum : unsigned {
@@ -103,8 +114,7 @@ enum : unsigned {
     KN_BS0 = 512u,   // Sigma0: two of three rotations via IMAD.WIDE
     KN_T1X = 1024u,  // t1 = IMAD(IADD3(IMAD(h,1,W), Sigma1, K), 1, Ch): one ALU add, no IMAD with an immediate
     KN_SP = 4096u,   // register+register adds of the specialised parts (first schedule words, rounds 4..6) as IMAD
-                     // (adds with a constant-bank or immediate operand stay on the ALU: an IMAD with a
-                     //  non-register addend raises dispatch stalls, measured with c[] operands as well)
+                     // (adds with a constant-bank operand stay on the ALU: moving them loses, measured)
     KN_T1Z = 8192u,  // zero ALU adds in a round: t1 = IMAD(IMAD(h,1,IMAD(W,1v,K_imm)), 1, IMAD(Sigma1,1,Ch)); the
                      // immediate-carrying IMAD uses a separate VECTOR-register 1 (one_v) so that all the other
                      // IMADs keep their uniform-register 1 (an IMAD takes only one non-vector operand).
