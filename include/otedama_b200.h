@@ -207,6 +207,16 @@ int otd_work_from_v1_notify(const otd_v1_notify_t* notify, const char* extranonc
                             uint32_t extranonce2_size, double difficulty, uint32_t channel_id,
                             otd_work_t* work, uint8_t* scratch, size_t scratch_len, size_t* scratch_needed);
 
+/* Static, zero-communication partition of a work's search space over G devices
+ * (the reference's only parallelism is nonce striding inside one
+ * Worker, internal/miner/worker.go:51-60,279).  Device g of G gets, in order of
+ * preference: every G-th BIP-320 version index (version_mask set), else every
+ * G-th extranonce2 value (coinbase set), else the g-th of G contiguous nonce
+ * windows.  *out is a shallow copy of *in with the slice fields rewritten (it
+ * points at the same coinbase buffers).  OTD_EINVAL when g is out of range or
+ * the axis has fewer than G values. */
+int otd_work_partition(const otd_work_t* in, uint32_t g, uint32_t G, otd_work_t* out);
+
 /* ----------------------------------------------------------------- worker --
  * One worker per device: the GPU counterpart of *miner.Worker
  * (internal/miner/worker.go:91-212), constructed by engine.startMinerWorkers

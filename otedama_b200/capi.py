@@ -103,6 +103,7 @@ _SIGS = {
     "otd_work_from_v1_job": (c_int, [c_char_p, c_uint32, c_char_p, c_uint32, c_uint32, c_double, POINTER(CWork)]),
     "otd_work_from_v1_notify": (c_int, [POINTER(CV1Notify), c_char_p, c_uint32, c_double, c_uint32, POINTER(CWork),
                                         c_char_p, c_size_t, POINTER(c_size_t)]),
+    "otd_work_partition": (c_int, [POINTER(CWork), c_uint32, c_uint32, POINTER(CWork)]),
     "otd_worker_create": (c_void_p, [c_int, POINTER(CWorkerConfig)]),
     "otd_worker_set_work": (c_int64, [c_void_p, POINTER(CWork)]),
     "otd_worker_poll_shares": (c_int, [c_void_p, POINTER(CShare), c_int, c_int]),

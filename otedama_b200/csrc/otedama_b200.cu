@@ -616,6 +616,33 @@ static int copy_work(const otd_work_t* in, WorkCopy* wc)
     return OTD_OK;
 }
 
+extern "C" int otd_work_partition(const otd_work_t* in, uint32_t g, uint32_t G, otd_work_t* out)
+{
+    if (!in || !out || G == 0 || g >= G) return fail(OTD_EINVAL, "otd_work_partition: bad argument");
+    WorkCopy wc;  // validates the input and resolves defaults (counts, strides)
+    int rc = copy_work(in, &wc);
+    if (rc) return rc;
+    otd_work_t w = *in;
+    if (in->version_mask) {
+        if (wc.n_ver < G) return fail(OTD_EINVAL, "otd_work_partition: fewer version indices than devices");
+        w.version_begin = in->version_begin + g * wc.ver_stride;
+        w.version_stride = wc.ver_stride * G;
+        w.version_count = (uint32_t)((wc.n_ver - g + G - 1) / G);
+    } else if (in->coinb1) {
+        if (wc.n_en2 < G) return fail(OTD_EINVAL, "otd_work_partition: fewer extranonce2 values than devices");
+        w.extranonce2_begin = in->extranonce2_begin + (uint64_t)g * wc.en2_stride;
+        w.extranonce2_stride = wc.en2_stride * G;
+        w.extranonce2_count = (wc.n_en2 - g + G - 1) / G;
+    } else {
+        if (wc.nonce_count < G) return fail(OTD_EINVAL, "otd_work_partition: fewer nonces than devices");
+        const uint64_t lo = wc.nonce_count * g / G, hi = wc.nonce_count * (g + 1) / G;
+        w.nonce_begin = in->nonce_begin + (uint32_t)lo;
+        w.nonce_count = hi - lo;
+    }
+    *out = w;
+    return OTD_OK;
+}
+
 // ------------------------------------------------------------------ engine --
 struct RunStats {
     uint64_t hashes = 0, launches = 0, candidates = 0, found = 0, ring_dropped = 0;

@@ -117,3 +117,20 @@ def work_from_v1_notify(params, extranonce1_hex: str, extranonce2_size: int, dif
     w.extranonce2_count = extranonce2_count or cw.extranonce2_count
     w.extranonce2_stride = extranonce2_stride
     return w
+
+
+def partition_work(work: miner.Work, g: int, G: int) -> miner.Work:
+    """The slice of `work` that device g of G searches (otd_work_partition): version indices,
+    else extranonce2 values, else a contiguous nonce window."""
+    import copy
+    cw, keep = work._c()
+    out = CWork()
+    if lib().otd_work_partition(ctypes.byref(cw), g, G, ctypes.byref(out)) < 0:
+        raise EngineError(capi.last_error())
+    del keep
+    w = copy.copy(work)
+    w.nonce_begin, w.nonce_count = out.nonce_begin, out.nonce_count
+    w.version_begin, w.version_count, w.version_stride = out.version_begin, out.version_count, out.version_stride
+    w.extranonce2_begin, w.extranonce2_count, w.extranonce2_stride = (out.extranonce2_begin, out.extranonce2_count,
+                                                                        out.extranonce2_stride)
+    return w

@@ -181,3 +181,64 @@ def test_block_1_nonce_is_found(eng, golden):
     r = miner.scan(miner.Work(header=h, nbits=h.bits, target=miner.target_from_nbits(h.bits), nonce_begin=n - 70000,
                               nonce_count=140000))
     assert [(s.nonce, s.hash[::-1].hex()) for s in r.shares] == [(n, rw["block1_hash_display"])]
+
+
+def _instances(w):
+    """(extranonce2, version index, nonce window) triples a Work covers, as sets of axis values."""
+    vers = set(range(w.version_begin, w.version_begin + max(1, w.version_count) * max(1, w.version_stride),
+                     max(1, w.version_stride))) if w.version_mask else {None}
+    en2 = set(range(w.extranonce2_begin, w.extranonce2_begin + w.extranonce2_count * max(1, w.extranonce2_stride),
+                    max(1, w.extranonce2_stride))) if w.coinb1 is not None else {None}
+    return vers, en2, (w.nonce_begin, w.nonce_begin + (w.nonce_count or 1 << 32))
+
+
+def test_partition_work_covers_the_space_exactly_once(eng):
+    engine, miner = eng
+    from otedama_b200 import workloads as W
+    c3, c4 = W.config3_v1(), W.config4_v2()
+    hdr = miner.Header(c4["version"], c4["prev_hash"], c4["merkle_root"], c4["time"], c4["bits"], 0)
+    t = b"\xff" * 32
+    for G in (1, 2, 3, 4, 8):
+        # version axis (configs[3]): every G-th index, whole mask
+        w = miner.Work(header=hdr, target=t, version_mask=c4["mask"])
+        parts = [engine.partition_work(w, g, G) for g in range(G)]
+        seen = [v for p in parts for v in _instances(p)[0]]
+        assert sorted(seen) == list(range(1 << 16)) and all(p.nonce_count == 0 for p in parts)
+        # ... also from an offset, with a stride, and a count not divisible by G
+        w = miner.Work(header=hdr, target=t, version_mask=c4["mask"], version_begin=5, version_stride=3, version_count=101)
+        seen = [v for g in range(G) for v in _instances(engine.partition_work(w, g, G))[0]]
+        assert sorted(seen) == list(range(5, 5 + 3 * 101, 3))
+        # extranonce2 axis (configs[2]/[4])
+        w = miner.Work(header=hdr, target=t, coinb1=c3["coinb1"], extranonce1=c3["extranonce1"], coinb2=c3["coinb2"],
+                       merkle_branches=c3["branches"], extranonce2_size=8, extranonce2_begin=7, extranonce2_count=1000,
+                       extranonce2_stride=2)
+        seen = [e for g in range(G) for e in _instances(engine.partition_work(w, g, G))[1]]
+        assert sorted(seen) == list(range(7, 7 + 2000, 2))
+        # plain header (configs[1] within one header): contiguous nonce windows
+        w = miner.Work(header=hdr, target=t, nonce_begin=1000, nonce_count=(1 << 32) - 1000)
+        wins = [_instances(engine.partition_work(w, g, G))[2] for g in range(G)]
+        assert wins[0][0] == 1000 and wins[-1][1] == 1 << 32
+        assert all(a[1] == b[0] for a, b in zip(wins, wins[1:]))
+    with pytest.raises(engine.EngineError):
+        engine.partition_work(miner.Work(header=hdr, target=t, nonce_count=3), 0, 4)
+    with pytest.raises(engine.EngineError):
+        engine.partition_work(miner.Work(header=hdr, target=t), 2, 2)
+
+
+@pytest.mark.gpu
+def test_partitioned_scans_reproduce_the_whole(eng, oracle):
+    engine, miner = eng
+    from otedama_b200 import capi, workloads as W
+    ndev = capi.lib().otd_device_count()
+    c3 = W.config3_v1()
+    t = oracle.target_from_difficulty(2.0 ** -20)
+    w = miner.Work(header=miner.Header(c3["version"], c3["prev_hash"], b"\x00" * 32, c3["time"], c3["bits"], 0), target=t,
+                   coinb1=c3["coinb1"], extranonce1=c3["extranonce1"], coinb2=c3["coinb2"], merkle_branches=c3["branches"],
+                   extranonce2_size=8, extranonce2_begin=3, extranonce2_count=21, nonce_count=1 << 14)
+    whole = miner.scan(w)
+    for G in (2, 3):
+        got = []
+        for g in range(G):
+            got += miner.scan(engine.partition_work(w, g, G), device=g % ndev).shares
+        assert sorted((s.extranonce2, s.nonce, s.hash) for s in got) == sorted((s.extranonce2, s.nonce, s.hash) for s in whole.shares)
+    assert len(whole.shares) > 100
