@@ -241,4 +241,4 @@ def test_partitioned_scans_reproduce_the_whole(eng, oracle):
         for g in range(G):
             got += miner.scan(engine.partition_work(w, g, G), device=g % ndev).shares
         assert sorted((s.extranonce2, s.nonce, s.hash) for s in got) == sorted((s.extranonce2, s.nonce, s.hash) for s in whole.shares)
-    assert len(whole.shares) > 100
+    assert len(whole.shares) > 50
