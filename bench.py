@@ -193,8 +193,12 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group(backend="gloo", rank=rank, world_size=world)
 
-    from otedama_b200 import build, capi, miner, workloads as W
-    build.build()
+    from otedama_b200 import build
+    if rank == 0:
+        build.build()          # no-op when the in-tree .so matches the sources (content hash)
+    if dist:
+        dist.barrier()         # nobody loads the library while rank 0 might still be linking it
+    from otedama_b200 import capi, miner, workloads as W
     ndev = capi.check(capi.lib().otd_device_count())
     if ndev <= 0:
         raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
