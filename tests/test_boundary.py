@@ -185,3 +185,12 @@ def test_missing_library_fails_loudly(product, monkeypatch):
     monkeypatch.setattr(capi, "LIB_PATH", "/nonexistent/libotedama_b200.so")
     with pytest.raises(capi.OtdError, match="no CPU fallback"):
         capi.lib()
+
+
+def test_no_undeclared_c_symbols_are_exported(product):
+    """The other direction: every unmangled otd_* symbol the library exports is declared in the header."""
+    import subprocess
+    from otedama_b200 import capi
+    out = subprocess.run(["nm", "-D", "--defined-only", capi.LIB_PATH], capture_output=True, text=True).stdout
+    exported = {line.split()[-1] for line in out.splitlines() if line.split() and line.split()[-1].startswith("otd_")}
+    assert exported == set(capi.declared_symbols())
