@@ -29,7 +29,9 @@ enum IntPeakMode {
     IPM_ALU2_FMA_IMM = 15,   // 1 SHF + 1 LOP3 : 1 IMAD with a 32-bit immediate addend
     IPM_ALU2_FMA_CONST = 16, // 1 SHF + 1 LOP3 : 1 IMAD with a constant-bank (kernel parameter) addend
     IPM_ALU2_FMA_PAIR = 17,  // 2 SHF + 2 LOP3 : 2 dependent IMADs back to back
-    IPM_COUNT = 18
+    IPM_ALU2_HI = 18,        // 1 SHF + 1 LOP3 : 1 IMAD.HI (does the high-half multiply co-issue?)
+    IPM_ALU4_ROT = 19,       // 2 SHF + 2 LOP3 : 1 rotation built as IMAD.HI + IMAD (x*m hi, then x*m + hi)
+    IPM_COUNT = 20
 };
 
 #if defined(__CUDACC__)
@@ -44,7 +46,8 @@ __host__ __device__ constexpr int ip_ops_per_step(int mode)
            : (mode == IPM_ALU_FMA || mode == IPM_ALU_WIDE)                        ? 2
            : (mode == IPM_ALU2_WIDE || mode == IPM_ALU2_FMA || mode == IPM_ALU2_FMA_IMM ||
               mode == IPM_ALU2_FMA_CONST)                                         ? 3
-           : (mode == IPM_ALU2_FMA_PAIR)                                          ? 6
+           : (mode == IPM_ALU2_FMA_PAIR || mode == IPM_ALU4_ROT)                  ? 6
+           : (mode == IPM_ALU2_HI)                                                ? 3
            : (mode == IPM_ALU_WIDE_FMA)                                           ? 4
                                                                                   : 1;
 }
@@ -140,6 +143,17 @@ __global__ void __launch_bounds__(1024) int_peak_kernel(int iters, uint32_t one,
                     asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
                     asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(z[c]));
                     asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(y[c]) : "r"(one), "r"(x[c]));
+                } else if (MODE == IPM_ALU2_HI) {
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("mul.hi.u32 %0, %0, %1;" : "+r"(y[c]) : "r"(seed));
+                } else if (MODE == IPM_ALU4_ROT) {
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("shf.r.wrap.b32 %0, %0, %0, 11;" : "+r"(x[c]));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[c]) : "r"(y[c]), "r"(z[c]));
+                    asm volatile("{ .reg .u32 hi;\n mul.hi.u32 hi, %0, %1;\n mad.lo.u32 %0, %0, %1, hi; }"
+                                 : "+r"(y[c]) : "r"(seed));
                 } else if (MODE == IPM_ALU_WIDE_FMA) {
                     asm volatile("shf.r.wrap.b32 %0, %0, %0, 7;" : "+r"(x[c]));
                     asm volatile("{ .reg .u64 w;\n mul.wide.u32 w, %0, %2;\n mov.b64 {%0, %1}, w; }"

@@ -1333,7 +1333,7 @@ extern "C" int otd_worker_destroy(otd_worker_t* w)
 static const char* kIntPeakNames[IPM_COUNT] = {"lop3", "shf", "iadd3", "imad", "mix_alu",
                                                "mix_dual", "mix_dual1", "imad_wide", "prmt", "alu_fma", "imad_hi",
                                                "alu_wide", "alu2_wide", "alu2_fma", "alu_wide_fma",
-                                               "alu2_fma_imm", "alu2_fma_const", "alu2_fma_pair"};
+                                               "alu2_fma_imm", "alu2_fma_const", "alu2_fma_pair", "alu2_hi", "alu4_rot"};
 
 extern "C" int otd_int_peak_modes(char (*names)[32], int max_names)
 {
@@ -1374,7 +1374,7 @@ extern "C" int otd_int_peak(int device_index, int mode, int iters, double* ops_p
     static const fn_t fns[IPM_COUNT] = {launch_peak<0>, launch_peak<1>, launch_peak<2>, launch_peak<3>, launch_peak<4>,
                                         launch_peak<5>, launch_peak<6>, launch_peak<7>, launch_peak<8>, launch_peak<9>, launch_peak<10>,
                                         launch_peak<11>, launch_peak<12>, launch_peak<13>, launch_peak<14>,
-                                        launch_peak<15>, launch_peak<16>, launch_peak<17>};
+                                        launch_peak<15>, launch_peak<16>, launch_peak<17>, launch_peak<18>, launch_peak<19>};
     cudaError_t e = cudaSuccess;
     for (int w = 0; w < 2 && e == cudaSuccess; w++) e = fns[mode](grid, iters / 4 + 1, d_sink, d_cyc, st);  // warm-up
     float ms = 0;
