@@ -1,0 +1,78 @@
+"""Property tests (hypothesis) of the host-side helpers behind the C ABI against the oracle's
+restatement of internal/miner/sha256d.go:134-257 — same value or same error, for every input class
+hypothesis likes to try (subnormals, huge exponents, NaN/inf, boundary nBits).  CPU only."""
+import struct
+
+import pytest
+
+hyp = pytest.importorskip("hypothesis")
+from hypothesis import given, settings, strategies as st  # noqa: E402
+
+SET = settings(max_examples=400, deadline=None)
+
+
+def _both(fn_c, fn_o, exc_c, exc_o, x):
+    try:
+        a = fn_c(x)
+    except exc_c:
+        a = None
+    try:
+        b = fn_o(x)
+    except exc_o:
+        b = None
+    return a, b
+
+
+@SET
+@given(st.integers(min_value=0, max_value=0xFFFFFFFF))
+def test_target_from_nbits_matches_oracle(product, oracle, nbits):
+    from otedama_b200 import miner
+    a, b = _both(miner.target_from_nbits, oracle.target_from_nbits, miner.MinerError, oracle.OracleError, nbits)
+    assert a == b
+    if a is not None:
+        # NBitsFromTarget is a left inverse up to the reference's documented normalisation
+        assert miner.nbits_from_target(a) == oracle.nbits_from_target(a)
+        assert miner.less_or_equal(a, a)
+
+
+@SET
+@given(st.floats(allow_nan=True, allow_infinity=True, allow_subnormal=True, width=64))
+def test_target_from_difficulty_matches_oracle(product, oracle, d):
+    from otedama_b200 import miner
+    a, b = _both(miner.target_from_difficulty, oracle.target_from_difficulty, miner.MinerError, oracle.OracleError, d)
+    assert a == b, d
+
+
+@SET
+@given(st.floats(min_value=1e-9, max_value=1e12), st.integers(min_value=0, max_value=0xFFFFFFFF))
+def test_v1_job_target_is_share_target_when_it_exists(product, oracle, diff, nbits):
+    from otedama_b200 import engine
+    try:
+        block = oracle.target_from_nbits(nbits)
+    except oracle.OracleError:
+        with pytest.raises(engine.EngineError):
+            engine.v1_job_target(nbits, diff)
+        return
+    try:
+        want = oracle.target_from_difficulty(diff)
+    except oracle.OracleError:
+        want = block
+    assert engine.v1_job_target(nbits, diff) == want
+
+
+@SET
+@given(st.binary(min_size=80, max_size=80))
+def test_header_roundtrip_and_layout(product, oracle, raw):
+    from otedama_b200 import miner
+    h = miner.parse_header(raw)
+    assert h.bytes() == raw
+    assert h.nonce == struct.unpack_from("<I", raw, 76)[0] and h.version == struct.unpack_from("<I", raw, 0)[0]
+    oh = oracle.Header.parse(raw)
+    assert (oh.version, oh.time, oh.bits, oh.nonce) == (h.version, h.time, h.bits, h.nonce)
+
+
+@SET
+@given(st.binary(min_size=32, max_size=32), st.binary(min_size=32, max_size=32))
+def test_less_or_equal_is_the_little_endian_integer_order(product, a, b):
+    from otedama_b200 import miner
+    assert miner.less_or_equal(a, b) == (int.from_bytes(a, "little") <= int.from_bytes(b, "little"))
