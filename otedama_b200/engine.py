@@ -134,3 +134,60 @@ def partition_work(work: miner.Work, g: int, G: int) -> miner.Work:
     w.extranonce2_begin, w.extranonce2_count, w.extranonce2_stride = (out.extranonce2_begin, out.extranonce2_count,
                                                                         out.extranonce2_stride)
     return w
+
+
+# ----------------------------------------------------------------------------
+# startMinerWorkers / mergeShares  (internal/engine/setup.go:56-78, fanin.go:20-68)
+# ----------------------------------------------------------------------------
+def start_miner_workers(devices, log=lambda level, msg: None, cfg: "miner.WorkerConfig | None" = None):
+    """One started worker per SHA256d-capable device, in device order, plus one merged share source.
+    Devices without the capability are skipped; none left is an error, as in the reference.
+    The caller owns shutdown (``for w in workers: w.stop()``)."""
+    import dataclasses
+    workers = []
+    try:
+        for dev in devices:
+            if not dev.capabilities().sha256d:
+                continue
+            c = dataclasses.replace(cfg) if cfg is not None else miner.default_worker_config()
+            c.device = getattr(dev, "index", c.device)
+            workers.append(miner.Worker(c).start())
+            log("info", f"engine: worker for {dev.identity()}")
+    except Exception:
+        for w in workers:
+            w.stop()
+        raise
+    if not workers:
+        raise EngineError("engine: no SHA256d-capable devices found")
+    return workers, MergedShares(workers)
+
+
+class MergedShares:
+    """mergeShares: the fan-in of every worker's share queue.  The Go version is a channel fed by one
+    goroutine per worker; here ``poll`` drains the workers round-robin so that no device starves
+    another, and returns when something arrived or the timeout passed."""
+
+    def __init__(self, workers):
+        self._workers = list(workers)
+        self._next = 0
+
+    def poll(self, max_shares: int = 256, timeout_ms: int = 0):
+        import time
+        deadline = time.monotonic() + timeout_ms / 1000.0
+        out = []
+        n = len(self._workers)
+        while True:
+            for k in range(n):
+                w = self._workers[(self._next + k) % n]
+                room = max_shares - len(out)
+                if room <= 0:
+                    break
+                out.extend(w.poll_shares(room, 0))
+            self._next = (self._next + 1) % max(n, 1)
+            if out or time.monotonic() >= deadline:
+                return out
+            # block briefly on one worker's queue instead of spinning
+            w = self._workers[self._next]
+            out.extend(w.poll_shares(max_shares, min(5, max(1, int((deadline - time.monotonic()) * 1000)))))
+            if out:
+                return out

@@ -242,3 +242,53 @@ def test_partitioned_scans_reproduce_the_whole(eng, oracle):
             got += miner.scan(engine.partition_work(w, g, G), device=g % ndev).shares
         assert sorted((s.extranonce2, s.nonce, s.hash) for s in got) == sorted((s.extranonce2, s.nonce, s.hash) for s in whole.shares)
     assert len(whole.shares) > 50
+
+
+# -- startMinerWorkers / mergeShares (internal/engine/setup.go:56-78; run_test.go:2443-2468) -----------------------
+class _NoSha256dDevice:
+    """run_test.go:2443-2453: a GPU that can do general compute but not SHA-256d."""
+
+    def identity(self):
+        from otedama_b200 import hal
+        return hal.Identity("gpu-0", hal.FAMILY_GPU, "", "")
+
+    def capabilities(self):
+        from otedama_b200 import hal
+        return hal.Capabilities(sha256d=False, general_compute=True)
+
+
+def test_start_miner_workers_no_sha256d_devices(eng):
+    engine, miner = eng
+    with pytest.raises(engine.EngineError, match="SHA256d"):
+        engine.start_miner_workers([_NoSha256dDevice()])
+    with pytest.raises(engine.EngineError, match="SHA256d"):
+        engine.start_miner_workers([])
+
+
+@pytest.mark.gpu
+def test_start_miner_workers_one_per_device_and_merged_shares(eng, oracle):
+    from otedama_b200 import hal
+    engine, miner = eng
+    devices = [_NoSha256dDevice()] + hal.CudaDriver().enumerate()
+    logged = []
+    workers, shares = engine.start_miner_workers(devices, log=lambda lv, m: logged.append((lv, m)))
+    try:
+        assert len(workers) == len(devices) - 1 and len(logged) == len(workers)
+        assert [w.device_id() for w in workers] == [d.identity().id for d in devices[1:]]
+        job = engine.NewMiningJob(channel_id=1, job_id=7, version=0x20000000, merkle_root=bytes(range(32)))
+        target = oracle.target_from_difficulty(1 / 65536.0)
+        engine.update_work(workers, job, 1, b"\x11" * 32, 0x1D00FFFF, 0x60000000, target)
+        got = []
+        for _ in range(400):
+            got += shares.poll(256, 50)
+            if len(got) >= 64:
+                break
+        assert len(got) >= 64
+        ids = {w.device_id() for w in workers}
+        for s in got:
+            assert s.device_id in ids and s.job_id == 7
+            h = oracle.Header(0x20000000, b"\x11" * 32, bytes(range(32)), s.ntime, 0x1D00FFFF, s.nonce)
+            assert oracle.hash_header(h) == s.hash and oracle.less_or_equal(s.hash, target)
+    finally:
+        for w in workers:
+            w.stop()
