@@ -970,7 +970,10 @@ static int pool_engine(int dev, Engine** out, std::mutex** lock)
     if (!g_pool[dev]) {
         std::unique_ptr<Engine> e(new Engine());
         rc = e->init(dev, 1u << 16);
-        if (rc) return rc;
+        if (rc) {
+            e->destroy();  // release whatever init got before it failed
+            return rc;
+        }
         g_pool[dev] = std::move(e);
     }
     *out = g_pool[dev].get();
@@ -1363,19 +1366,18 @@ extern "C" int otd_int_peak(int device_index, int mode, int iters, double* ops_p
     const int grid = sms;
     uint32_t* d_sink = nullptr;
     long long* d_cyc = nullptr;
-    CU_TRY(cudaMalloc(&d_sink, sizeof(uint32_t)));
-    CU_TRY(cudaMalloc(&d_cyc, sizeof(long long)));
-    cudaStream_t st;
-    CU_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
-    cudaEvent_t e0, e1;
-    CU_TRY(cudaEventCreate(&e0));
-    CU_TRY(cudaEventCreate(&e1));
+    cudaStream_t st = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    cudaError_t e = cudaMalloc(&d_sink, sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMalloc(&d_cyc, sizeof(long long));
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreate(&e0);
+    if (e == cudaSuccess) e = cudaEventCreate(&e1);
     typedef cudaError_t (*fn_t)(int, int, uint32_t*, long long*, cudaStream_t);
     static const fn_t fns[IPM_COUNT] = {launch_peak<0>, launch_peak<1>, launch_peak<2>, launch_peak<3>, launch_peak<4>,
                                         launch_peak<5>, launch_peak<6>, launch_peak<7>, launch_peak<8>, launch_peak<9>, launch_peak<10>,
                                         launch_peak<11>, launch_peak<12>, launch_peak<13>, launch_peak<14>,
                                         launch_peak<15>, launch_peak<16>, launch_peak<17>, launch_peak<18>, launch_peak<19>};
-    cudaError_t e = cudaSuccess;
     for (int w = 0; w < 2 && e == cudaSuccess; w++) e = fns[mode](grid, iters / 4 + 1, d_sink, d_cyc, st);  // warm-up
     float ms = 0;
     long long cyc = 0;
@@ -1385,7 +1387,11 @@ extern "C" int otd_int_peak(int device_index, int mode, int iters, double* ops_p
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
     if (e == cudaSuccess) e = cudaMemcpy(&cyc, d_cyc, sizeof cyc, cudaMemcpyDeviceToHost);
-    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st); cudaFree(d_sink); cudaFree(d_cyc);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (st) cudaStreamDestroy(st);
+    cudaFree(d_sink);
+    cudaFree(d_cyc);
     if (e != cudaSuccess) return fail(OTD_ECUDA, std::string("otd_int_peak: ") + cudaGetErrorString(e));
     const double ops = (double)grid * 1024.0 * (double)iters * kIpUnroll * kIpChains * ip_ops_per_step(mode);
     if (ops_per_s) *ops_per_s = ops / (ms * 1e-3);
