@@ -207,6 +207,26 @@ int otd_work_from_v1_notify(const otd_v1_notify_t* notify, const char* extranonc
                             uint32_t extranonce2_size, double difficulty, uint32_t channel_id,
                             otd_work_t* work, uint8_t* scratch, size_t scratch_len, size_t* scratch_needed);
 
+/* A found share -> the hex fields of Stratum V1 mining.submit
+ * (["worker", job_id, extranonce2, ntime, nonce] and, with version rolling, the
+ * BIP-310 sixth field version_bits).  Replaces the body of session.Submit's
+ * parameter formatting (internal/poolproto/stratumv1/stratumv1.go:336-346),
+ * which today pads extranonce2 with zeros because the reference never rolls it:
+ *   extranonce2_hex  = the extranonce2_size bytes that were placed in the coinbase
+ *                      (little-endian counter, like otd_work_t says), lower-case hex;
+ *   ntime_hex, nonce_hex = "%08x" of the u32 values, as the reference formats them;
+ *   version_bits_hex = "%08x" of share.version & version_mask ("" when the mask is 0).
+ * extranonce2_size 0 (no coinbase in the work) gives an empty extranonce2_hex.
+ * OTD_EINVAL for a NULL argument or extranonce2_size > 16. */
+typedef struct {
+    char extranonce2_hex[33];
+    char ntime_hex[9];
+    char nonce_hex[9];
+    char version_bits_hex[9];
+} otd_v1_submit_t;
+int otd_share_to_v1_submit(const otd_share_t* share, uint32_t extranonce2_size, uint32_t version_mask,
+                           otd_v1_submit_t* out);
+
 /* Static, zero-communication partition of a work's search space over G devices
  * (the reference's only parallelism is nonce striding inside one
  * Worker, internal/miner/worker.go:51-60,279).  Device g of G gets, in order of

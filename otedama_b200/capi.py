@@ -68,6 +68,11 @@ class CShare(Structure):
                 ("work_seq", c_uint64), ("device_index", c_int32), ("reserved", c_int32)]
 
 
+class CV1Submit(Structure):
+    _fields_ = [("extranonce2_hex", c_char * 33), ("ntime_hex", c_char * 9), ("nonce_hex", c_char * 9),
+                ("version_bits_hex", c_char * 9)]
+
+
 class CWorkerConfig(Structure):
     _fields_ = [("ring_capacity", c_uint32), ("queue_capacity", c_uint32), ("launch_log2", c_uint32),
                 ("kernel_variant", c_int32)]
@@ -104,6 +109,7 @@ _SIGS = {
     "otd_work_from_v1_notify": (c_int, [POINTER(CV1Notify), c_char_p, c_uint32, c_double, c_uint32, POINTER(CWork),
                                         c_char_p, c_size_t, POINTER(c_size_t)]),
     "otd_work_partition": (c_int, [POINTER(CWork), c_uint32, c_uint32, POINTER(CWork)]),
+    "otd_share_to_v1_submit": (c_int, [POINTER(CShare), c_uint32, c_uint32, POINTER(CV1Submit)]),
     "otd_worker_create": (c_void_p, [c_int, POINTER(CWorkerConfig)]),
     "otd_worker_set_work": (c_int64, [c_void_p, POINTER(CWork)]),
     "otd_worker_poll_shares": (c_int, [c_void_p, POINTER(CShare), c_int, c_int]),

@@ -643,6 +643,22 @@ extern "C" int otd_work_partition(const otd_work_t* in, uint32_t g, uint32_t G, 
     return OTD_OK;
 }
 
+extern "C" int otd_share_to_v1_submit(const otd_share_t* share, uint32_t extranonce2_size, uint32_t version_mask,
+                                      otd_v1_submit_t* out)
+{
+    if (!share || !out) return fail(OTD_EINVAL, "otd_share_to_v1_submit: NULL argument");
+    if (extranonce2_size > 16) return fail(OTD_EINVAL, "otd_share_to_v1_submit: extranonce2_size exceeds 16");
+    memset(out, 0, sizeof *out);
+    for (uint32_t i = 0; i < extranonce2_size; i++) {
+        const unsigned b = i < 8 ? (unsigned)(share->extranonce2 >> (8 * i)) & 0xffu : 0u;  // same bytes as the coinbase got
+        snprintf(out->extranonce2_hex + 2 * i, 3, "%02x", b);
+    }
+    snprintf(out->ntime_hex, sizeof out->ntime_hex, "%08x", share->ntime);
+    snprintf(out->nonce_hex, sizeof out->nonce_hex, "%08x", share->nonce);
+    if (version_mask) snprintf(out->version_bits_hex, sizeof out->version_bits_hex, "%08x", share->version & version_mask);
+    return OTD_OK;
+}
+
 // ------------------------------------------------------------------ engine --
 struct RunStats {
     uint64_t hashes = 0, launches = 0, candidates = 0, found = 0, ring_dropped = 0;

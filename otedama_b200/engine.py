@@ -119,6 +119,22 @@ def work_from_v1_notify(params, extranonce1_hex: str, extranonce2_size: int, dif
     return w
 
 
+def v1_submit_params(share: miner.Share, work: miner.Work, worker_name: str = "otedama"):
+    """The mining.submit parameter list for a share of a V1 work unit (stratumv1.go:336-346 with the
+    rolled extranonce2 instead of zero padding; a sixth BIP-310 version_bits field when rolling)."""
+    cs = capi.CShare(share.channel_id, share.job_id, share.nonce, share.ntime, share.version,
+                     (ctypes.c_uint8 * 32)(*share.hash), share.extranonce2, share.work_seq, 0, 0)
+    out = capi.CV1Submit()
+    size = work.extranonce2_size if work.coinb1 is not None else 0
+    if lib().otd_share_to_v1_submit(ctypes.byref(cs), size, work.version_mask, ctypes.byref(out)) < 0:
+        raise EngineError(capi.last_error())
+    params = [worker_name, str(share.job_id), out.extranonce2_hex.decode(), out.ntime_hex.decode(),
+              out.nonce_hex.decode()]
+    if work.version_mask:
+        params.append(out.version_bits_hex.decode())
+    return params
+
+
 def partition_work(work: miner.Work, g: int, G: int) -> miner.Work:
     """The slice of `work` that device g of G searches (otd_work_partition): version indices,
     else extranonce2 values, else a contiguous nonce window."""

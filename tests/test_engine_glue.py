@@ -169,6 +169,10 @@ def test_block_170_is_found_from_its_notify_form(eng, oracle, golden):
     assert r.hashes == 4 << 21 and r.launches == 4
     inst = miner.prepare_instances(w, 2, 1)[0]
     assert inst.merkle_root[::-1].hex() == b["merkle_root_display"] and inst.extranonce2 == 2
+    # ... and what goes back to the pool rebuilds the mined coinbase
+    sub = engine.v1_submit_params(r.shares[0], w)
+    assert sub == ["otedama", "170", "02", "%08x" % b["time"], "%08x" % b["nonce"]]
+    assert cb[:k] + bytes.fromhex(sub[2]) + cb[k + 1:] == cb
 
 
 @pytest.mark.gpu
@@ -292,3 +296,46 @@ def test_start_miner_workers_one_per_device_and_merged_shares(eng, oracle):
     finally:
         for w in workers:
             w.stop()
+
+
+# -- share -> mining.submit fields (stratumv1.go:336-346) ----------------------------------------------------------
+def test_v1_submit_params_format(eng, oracle):
+    engine, miner = eng
+    sh = miner.Share(channel_id=1, job_id=77, nonce=0x0000BEEF, ntime=0x60000001, version=0x2ABCE000, hash=b"\x00" * 32,
+                     extranonce2=0x0102030405)
+    for size in (4, 5, 8, 12, 16):
+        w = miner.Work(coinb1=b"\x01", extranonce2_size=size)
+        p = engine.v1_submit_params(sh, w)
+        assert p[:2] == ["otedama", "77"] and p[3:] == ["60000001", "0000beef"]
+        # the same bytes the coinbase was hashed with (oracle's insertion rule), low `size` bytes of the counter
+        assert p[2] == oracle.extranonce2_bytes(0x0102030405 & ((1 << (8 * size)) - 1), size).hex()
+    assert engine.v1_submit_params(sh, miner.Work())[2] == ""              # no coinbase in the work: nothing rolled
+    rolled = engine.v1_submit_params(sh, miner.Work(coinb1=b"\x01", extranonce2_size=4, version_mask=0x1FFFE000))
+    assert rolled[5] == "%08x" % (0x2ABCE000 & 0x1FFFE000) and len(rolled) == 6
+    with pytest.raises(engine.EngineError, match="exceeds 16"):
+        engine.v1_submit_params(sh, miner.Work(coinb1=b"\x01", extranonce2_size=17))
+
+
+@pytest.mark.gpu
+def test_pool_side_check_of_submitted_fields(eng, oracle):
+    """What a pool does with mining.submit: rebuild coinbase, merkle root and header from the job it
+    sent plus the five (six) submitted fields, hash, compare with the share target."""
+    from otedama_b200 import workloads as W
+    engine, miner = eng
+    c3 = W.config3_v1()
+    mask = 0x1FFFE000
+    target = miner.target_from_difficulty(2.0 ** -16)
+    w = miner.Work(job_id=31, header=miner.Header(c3["version"], c3["prev_hash"], b"\x00" * 32, c3["time"], c3["bits"], 0),
+                   nbits=c3["bits"], target=target, nonce_count=1 << 18, coinb1=c3["coinb1"],
+                   extranonce1=c3["extranonce1"], coinb2=c3["coinb2"], merkle_branches=c3["branches"],
+                   extranonce2_size=8, extranonce2_begin=0xFFFFFFFE, extranonce2_count=4, version_mask=mask,
+                   version_begin=65533, version_count=3)
+    r = miner.scan(w)
+    assert len(r.shares) > 10
+    for s in r.shares:
+        _, job, en2_hex, ntime_hex, nonce_hex, vbits_hex = engine.v1_submit_params(s, w)
+        assert job == "31"
+        root = oracle.v1_merkle_root(c3["coinb1"], c3["extranonce1"], bytes.fromhex(en2_hex), c3["coinb2"], c3["branches"])
+        version = (c3["version"] & ~mask) | (int(vbits_hex, 16) & mask)
+        h = oracle.Header(version, c3["prev_hash"], root, int(ntime_hex, 16), c3["bits"], int(nonce_hex, 16))
+        assert oracle.hash_header(h) == s.hash and oracle.less_or_equal(s.hash, target)
