@@ -194,3 +194,36 @@ def test_no_undeclared_c_symbols_are_exported(product):
     out = subprocess.run(["nm", "-D", "--defined-only", capi.LIB_PATH], capture_output=True, text=True).stdout
     exported = {line.split()[-1] for line in out.splitlines() if line.split() and line.split()[-1].startswith("otd_")}
     assert exported == set(capi.declared_symbols())
+
+
+# -- work validation (the checks every entry point runs before touching a device) ---------------------------------
+def test_work_validation_errors(product):
+    """SetWork cannot fail in the reference because bad jobs are rejected before it (run.go:1274-1279,
+    1341-1344); the search-space extension adds fields that can be inconsistent, and those are refused with a
+    message.  otd_work_partition runs the same validation without needing a device."""
+    from otedama_b200 import engine, miner
+    ok = dict(coinb1=b"\x01\x02", extranonce2_size=4, extranonce2_count=8)
+    bad = [
+        (dict(nonce_begin=0xFFFFFFFF, nonce_count=2), "nonce window exceeds 2^32"),
+        (dict(nonce_begin=1, nonce_count=1 << 32), "nonce window exceeds 2^32"),
+        (dict(version_count=2), "without a version_mask"),
+        (dict(version_mask=0x6000, version_begin=4), "version_begin outside"),
+        (dict(version_mask=0x6000, version_count=5), "version_count exceeds"),
+        (dict(version_mask=0x6000, version_begin=1, version_stride=2, version_count=3), "version_count exceeds"),
+        (dict(ok, extranonce2_size=17), "extranonce2_size > 16"),
+        (dict(ok, extranonce2_count=0), "extranonce2_count must be >= 1"),
+        (dict(ok, extranonce2_size=1, extranonce2_count=257), "does not fit extranonce2_size"),
+        (dict(ok, extranonce2_size=2, extranonce2_begin=65536, extranonce2_count=1), "does not fit extranonce2_size"),
+        (dict(ok, extranonce2_size=2, extranonce2_begin=1, extranonce2_stride=1 << 15, extranonce2_count=3), "does not fit"),
+        (dict(ok, coinb2=b"\x00" * ((1 << 20) + 1)), "coinbase too large"),
+        (dict(ok, merkle_branches=[b"\x00" * 32] * 65), "coinbase too large"),
+        (dict(ok, extranonce2_size=8, extranonce2_count=1 << 50, version_mask=0x1FFFE000), "search space too large"),
+    ]
+    for fields, msg in bad:
+        with pytest.raises(engine.EngineError, match=msg.replace("^", r"\^")):
+            engine.partition_work(miner.Work(**fields), 0, 1)
+    # and the same work with consistent fields passes
+    for fields in (dict(nonce_begin=0xFFFFFFFF, nonce_count=1), dict(version_mask=0x6000, version_begin=3),
+                   dict(version_mask=0x6000, version_begin=1, version_stride=2, version_count=2),
+                   dict(ok, extranonce2_size=1, extranonce2_count=256), dict(ok, extranonce2_size=0, extranonce2_count=1)):
+        engine.partition_work(miner.Work(**fields), 0, 1)
