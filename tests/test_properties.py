@@ -76,3 +76,39 @@ def test_header_roundtrip_and_layout(product, oracle, raw):
 def test_less_or_equal_is_the_little_endian_integer_order(product, a, b):
     from otedama_b200 import miner
     assert miner.less_or_equal(a, b) == (int.from_bytes(a, "little") <= int.from_bytes(b, "little"))
+
+
+# -- static partition: whatever the axis, the G slices are disjoint and cover the work ----------------
+@settings(max_examples=300, deadline=None)
+@given(st.integers(1, 16), st.integers(0, 200), st.integers(1, 7), st.integers(1, 300), st.sampled_from(["version", "en2", "nonce"]))
+def test_partition_is_a_partition(product, G, begin, stride, count, axis):
+    from otedama_b200 import engine, miner
+    mask = 0x1FFFE000
+    if axis == "version":
+        w = miner.Work(version_mask=mask, version_begin=begin, version_stride=stride, version_count=count)
+        whole = list(range(begin, begin + stride * count, stride))
+    elif axis == "en2":
+        w = miner.Work(coinb1=b"\x01", extranonce2_size=8, extranonce2_begin=begin, extranonce2_stride=stride,
+                       extranonce2_count=count)
+        whole = list(range(begin, begin + stride * count, stride))
+    else:
+        w = miner.Work(nonce_begin=begin, nonce_count=count)
+        whole = list(range(begin, begin + count))
+    if count < G:
+        with pytest.raises(engine.EngineError, match="fewer"):
+            engine.partition_work(w, 0, G)
+        return
+    seen = []
+    for g in range(G):
+        p = engine.partition_work(w, g, G)
+        if axis == "version":
+            seen += range(p.version_begin, p.version_begin + p.version_stride * p.version_count, p.version_stride)
+            assert (p.nonce_begin, p.nonce_count) == (0, 0)
+        elif axis == "en2":
+            seen += range(p.extranonce2_begin, p.extranonce2_begin + p.extranonce2_stride * p.extranonce2_count,
+                          p.extranonce2_stride)
+        else:
+            seen += range(p.nonce_begin, p.nonce_begin + p.nonce_count)
+    assert sorted(seen) == whole
+    with pytest.raises(engine.EngineError):
+        engine.partition_work(w, G, G)
