@@ -281,8 +281,8 @@ def main():
         roofline = {"bound": "int-issue", "achieved": achieved / 1e12, "peak": peak_alu / 1e12,
                     "unit": "Tint-op/s", "frac": achieved / peak_alu, "traffic": 127488,
                     "note": ("achieved = per-GPU H/s x 2450 algorithmic 3-input integer ops/hash (SURVEY §8d); "
-                             "peak = ALU-pipe rate (SHF/LOP3/IADD3 at the SHA mix) measured on this GPU in this run, "
-                             "of measured; frac exceeds 1 because the kernel issues almost all of the ~650 adds/hash as IMAD on the "
+                             "peak = ALU-pipe rate (SHF/LOP3/IADD3 at the SHA mix) measured on this GPU in this run; "
+                             "frac exceeds 1 because the kernel issues almost all of the ~650 adds/hash as IMAD on the "
                              "FMA pipe, which a one-pipe roofline does not model; traffic = dram__bytes_read+write "
                              "(bytes) of one 2^30-candidate launch from ncu --set full "
                              "(profiles/r1_ncu_scan_kernel.csv): effectively none"),
