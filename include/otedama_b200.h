@@ -279,7 +279,11 @@ int otd_worker_wait_exhausted(otd_worker_t* w, int timeout_ms);
 int otd_worker_stats(otd_worker_t* w, otd_stats_t* out);        /* Stats()   worker.go:189-212 */
 int otd_worker_has_work(otd_worker_t* w);                       /* HasWork() worker.go:181-185 */
 int otd_worker_device_index(otd_worker_t* w);                   /* DeviceID() worker.go:176    */
-/* Stop (worker.go:156-165): aborts in-flight work, joins the host thread, frees. */
+/* Stop (worker.go:156-165): aborts in-flight work, joins the host thread, frees.
+ * All other calls on a handle may run concurrently with each other; destroy must
+ * be the last one — a caller parked in otd_worker_poll_shares has to return
+ * before the handle is destroyed (the Go shim waits for its forwarding goroutine,
+ * INTEGRATION.md §2), because the handle's memory is released here. */
 int otd_worker_destroy(otd_worker_t* w);
 
 /* ------------------------------------------------------- synchronous scan --
