@@ -12,6 +12,7 @@ import "C"
 
 import (
 	"context"
+	"fmt"
 	"sync/atomic"
 	"time"
 	"unsafe"
@@ -21,11 +22,17 @@ type GPUWorker struct {
 	h        *C.otd_worker_t
 	deviceID string
 	started  atomic.Bool
+	cancel   atomic.Pointer[context.CancelFunc]
 	done     chan struct{}
 }
 
-func NewGPUWorker(deviceIndex int, deviceID string) *GPUWorker {
-	return &GPUWorker{h: C.otd_worker_create(C.int(deviceIndex), nil), deviceID: deviceID, done: make(chan struct{})}
+// NewGPUWorker fails when the device cannot be opened (no CPU fallback behind it).
+func NewGPUWorker(deviceIndex int, deviceID string) (*GPUWorker, error) {
+	h := C.otd_worker_create(C.int(deviceIndex), nil)
+	if h == nil {
+		return nil, fmt.Errorf("miner: gpu worker %s: %s", deviceID, C.GoString(C.otd_last_error()))
+	}
+	return &GPUWorker{h: h, deviceID: deviceID, done: make(chan struct{})}, nil
 }
 
 // Start mirrors (*Worker).Start (worker.go:127-151): one goroutine parks in
@@ -35,11 +42,13 @@ func (w *GPUWorker) Start(ctx context.Context) <-chan Share {
 		panic("miner: Worker.Start called more than once")
 	}
 	shares := make(chan Share, 256)
+	inner, cancel := context.WithCancel(ctx) // Stop cancels this, like worker.go:131-132
+	w.cancel.Store(&cancel)
 	go func() {
 		defer close(w.done)
 		defer close(shares)
 		buf := make([]C.otd_share_t, 64)
-		for ctx.Err() == nil {
+		for inner.Err() == nil {
 			n := int(C.otd_worker_poll_shares(w.h, &buf[0], C.int(len(buf)), 100))
 			for i := 0; i < n; i++ {
 				s := Share{ChannelID: uint32(buf[i].channel_id), JobID: uint32(buf[i].job_id),
@@ -56,12 +65,18 @@ func (w *GPUWorker) Start(ctx context.Context) <-chan Share {
 	return shares
 }
 
-func (w *GPUWorker) Stop() { // worker.go:156-165
-	if w.started.Load() {
+// Stop mirrors (*Worker).Stop (worker.go:156-165): cancel, wait for the forwarding
+// goroutine to leave otd_worker_poll_shares (at most its 100 ms timeout), then free
+// the handle — destroy has to be the last call on it. Safe without Start.
+func (w *GPUWorker) Stop() {
+	if c := w.cancel.Load(); c != nil {
+		(*c)()
 		<-w.done
 	}
-	C.otd_worker_destroy(w.h)
-	w.h = nil
+	if w.h != nil {
+		C.otd_worker_destroy(w.h)
+		w.h = nil
+	}
 }
 
 // SetWork mirrors (*Worker).SetWork (worker.go:171-176); nil pauses the device.
