@@ -103,6 +103,32 @@ def test_equality_counts_as_a_share(miner):
         assert r.found == want
 
 
+def test_smallest_windows_and_the_zero_target(miner, oracle):
+    """Windows of one nonce (also the very last nonce, 0xFFFFFFFF), tiny ragged windows around a known
+    share, and the all-zero target, which nothing but an all-zero hash meets."""
+    f = W.genesis_fields()
+    t = miner.target_from_nbits(W.DIFF1_NBITS)
+    h = mheader(miner, f)
+    for v in variants(miner):
+        one = miner.scan(miner.Work(header=h, target=t, nonce_begin=W.GENESIS_NONCE, nonce_count=1), variant=v)
+        assert (one.hashes, [s.nonce for s in one.shares]) == (1, [W.GENESIS_NONCE])
+        miss = miner.scan(miner.Work(header=h, target=t, nonce_begin=W.GENESIS_NONCE + 1, nonce_count=1), variant=v)
+        assert (miss.hashes, miss.found) == (1, 0)
+        for before, count in ((0, 2), (1, 2), (255, 256), (256, 257), (299, 300), (4095, 4097)):
+            r = miner.scan(miner.Work(header=h, target=t, nonce_begin=W.GENESIS_NONCE - before, nonce_count=count),
+                           variant=v)
+            assert (r.hashes, [s.nonce for s in r.shares]) == (count, [W.GENESIS_NONCE])
+            r = miner.scan(miner.Work(header=h, target=t, nonce_begin=W.GENESIS_NONCE - before - count,
+                                      nonce_count=count), variant=v)       # window ends just before the share
+            assert (r.hashes, r.found) == (count, 0)
+    easy = b"\xff" * 32
+    last = miner.scan(miner.Work(header=h, target=easy, nonce_begin=0xFFFFFFFF, nonce_count=1))
+    hdr = oracle.Header(f["version"], f["prev_hash"], f["merkle_root"], f["time"], f["bits"], 0xFFFFFFFF)
+    assert [(s.nonce, s.hash) for s in last.shares] == [(0xFFFFFFFF, oracle.hash_header(hdr))]
+    zero = miner.scan(miner.Work(header=h, target=b"\x00" * 32, nonce_begin=W.GENESIS_NONCE - (1 << 20), nonce_count=1 << 21))
+    assert (zero.hashes, zero.found, zero.shares) == (1 << 21, 0, [])
+
+
 def test_dense_windows_match_golden_and_oracle(miner, oracle, golden):
     for case in golden["synthetic_windows"]["cases"]:
         f = W.config2_fields(case["index"])
