@@ -9,10 +9,11 @@ import time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from otedama_b200 import miner, workloads as W  # noqa: E402
 
+variant = int(sys.argv[1]) if len(sys.argv) > 1 else -1       # kernel variant index (-1 = default)
 f1, f2 = W.config2_fields(40), W.config2_fields(41)
 hard = (1).to_bytes(32, "little")
 lat = []
-with miner.Worker() as w:
+with miner.Worker(miner.WorkerConfig(kernel_variant=variant)) as w:
     for rep in range(12):
         a = miner.Work(job_id=1, header=miner.Header(**f1), target=hard, repeat=True)
         b = miner.Work(job_id=2 + rep, header=miner.Header(**f2), target=b"\xff" * 32, nonce_count=1 << 16)
