@@ -180,7 +180,8 @@ int otd_work_from_v1_job(const char* job_id, uint32_t channel_id, const uint8_t 
  * (north_star).  The reference's parseNotify keeps job id, prevhash,
  * version, nbits, ntime and DISCARDS coinb1 / coinb2 / merkle_branch
  * (internal/poolproto/stratumv1/parse.go:33-93), so this follows the public
- * Stratum V1 conventions ("parity unpinned"):
+ * Stratum V1 conventions ("parity unpinned" against the reference; pinned instead by
+ * the protocol documentation's own worked example and by block 170):
  *   params = [job_id, prevhash, coinb1, coinb2, merkle_branch[], version, nbits, ntime, clean_jobs]
  *   - prevhash: 64 hex chars, eight 4-byte words each byte-swapped with respect to
  *     header order (header bytes = each word reversed);

@@ -25,7 +25,9 @@
  *   orc_v1_merkle_root, orc_extranonce2_bytes, orc_bip320_version.
  * orc_v1_merkle_root is additionally anchored to public chain data that the
  * tests re-derive with hashlib (genesis coinbase -> genesis merkle root; block
- * 170: coinbase -> txid -> merkle fold -> header -> published block hash).
+ * 170: coinbase -> txid -> merkle fold -> header -> published block hash; the
+ * Stratum V1 documentation's worked example: notify + submit -> a hash with 34
+ * leading zero bits).
  *
  * Two compression back-ends are provided because Go's crypto/sha256
  * dispatches to SHA-NI on amd64 when the CPU has it: a portable scalar

@@ -175,6 +175,50 @@ def test_block_170_is_found_from_its_notify_form(eng, oracle, golden):
     assert cb[:k] + bytes.fromhex(sub[2]) + cb[k + 1:] == cb
 
 
+def _docs_example_work(engine, golden):
+    ex = golden["reference_vectors"]["real_world_anchors"]["stratum_docs_example"]
+    params = list(ex["notify_params"])
+    assert params[0] == "bf"
+    with pytest.raises(engine.EngineError, match="unparseable job ID"):   # like applyJob's Sscanf("%d"), run.go:1345-1348
+        engine.work_from_v1_notify(params, ex["subscribe_extranonce1"], ex["subscribe_extranonce2_size"], 1.0)
+    params[0] = str(0xBF)
+    en2 = int.from_bytes(bytes.fromhex(ex["submit_params"][2]), "little")
+    w = engine.work_from_v1_notify(params, ex["subscribe_extranonce1"], ex["subscribe_extranonce2_size"], 1.0,
+                                   extranonce2_begin=en2 - 1, extranonce2_count=3)
+    return ex, w
+
+
+def test_stratum_documentation_example_as_a_work_unit(eng, golden):
+    """The documentation's notify through otd_work_from_v1_notify: the header fields a miner must hash."""
+    engine, miner = eng
+    ex, w = _docs_example_work(engine, golden)
+    wire = bytes.fromhex(ex["notify_params"][1])
+    assert w.header.prev_hash == b"".join(wire[4 * i:4 * i + 4][::-1] for i in range(8))
+    assert w.header.prev_hash[-4:] == b"\x00" * 4                # header order: the hash's zero bytes come last
+    assert (w.header.version, w.header.bits, w.header.time) == (2, 0x1C2AC4AF, 0x504E86B9)
+    assert (w.job_id, w.extranonce1.hex(), w.extranonce2_size) == (0xBF, "08000002", 4)
+    assert w.coinb1.hex() == ex["notify_params"][2] and w.coinb2.hex() == ex["notify_params"][3] and not w.merkle_branches
+    assert w.target == miner.target_from_difficulty(1.0)
+
+
+@pytest.mark.gpu
+def test_stratum_documentation_example_share_is_found_and_submitted(eng, golden):
+    """... and on the device: rolling extranonce2 and scanning around the documented nonce finds exactly the
+    share the documentation submits, and the submit fields come back as documented."""
+    engine, miner = eng
+    ex, w = _docs_example_work(engine, golden)
+    sub = ex["submit_params"]
+    w.header.time = int(sub[3], 16)                              # the miner's rolled ntime
+    nonce = int(sub[4], 16)
+    w.nonce_begin, w.nonce_count = nonce - (1 << 20), 1 << 21
+    r = miner.scan(w)
+    assert r.hashes == 3 << 21
+    assert [(s.nonce, s.hash[::-1].hex()) for s in r.shares] == [(nonce, ex["hash_display"])]
+    inst = miner.prepare_instances(w, 1, 1)[0]
+    assert inst.merkle_root.hex() == ex["merkle_root_header_order"]
+    assert engine.v1_submit_params(r.shares[0], w, worker_name=sub[0]) == [sub[0], str(0xBF), sub[2], sub[3], sub[4]]
+
+
 @pytest.mark.gpu
 def test_block_1_nonce_is_found(eng, golden):
     engine, miner = eng

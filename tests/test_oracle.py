@@ -229,3 +229,29 @@ def test_real_world_anchors_pin_the_unpinned_subpaths(oracle, golden):
     oh = oracle.v1_header(params, b"", en2)
     oh.nonce = b["nonce"]
     assert oracle.hash_header(oh)[::-1].hex() == b["hash_display"]
+
+
+def test_stratum_documentation_example_pins_the_v1_wire_conventions(oracle, golden):
+    """The protocol documentation's own accepted share: notify + subscribe + submit -> a header whose hash has
+    34 leading zero bits, but only under the conventions the oracle (and the product) follow."""
+    import hashlib
+    ex = _rw(golden)["stratum_docs_example"]
+    params, sub = ex["notify_params"], ex["submit_params"]
+    en1, en2 = bytes.fromhex(ex["subscribe_extranonce1"]), bytes.fromhex(sub[2])
+    assert len(en2) == ex["subscribe_extranonce2_size"] and sub[1] == params[0]
+    h = oracle.v1_header(params, en1, en2)
+    assert h.merkle_root.hex() == ex["merkle_root_header_order"]
+    h.time, h.nonce = int(sub[3], 16), int(sub[4], 16)      # the miner rolled ntime; both big-endian hex of the u32
+    hh = oracle.hash_header(h)
+    assert hh[::-1].hex() == ex["hash_display"] == hashlib.sha256(hashlib.sha256(h.bytes()).digest()).digest()[::-1].hex()
+    assert oracle.less_or_equal(hh, oracle.target_from_difficulty(1.0))
+    # the extranonce2 bytes are the little-endian counter the product rolls: value 0x01000000 here
+    assert oracle.extranonce2_bytes(int.from_bytes(en2, "little"), 4) == en2
+    # any other reading of the wire form gives an ordinary hash
+    raw_prev = bytes.fromhex(params[1])
+    for prev in (raw_prev, raw_prev[::-1]):
+        bad = oracle.Header(h.version, prev, h.merkle_root, h.time, h.bits, h.nonce)
+        assert not oracle.hash_header(bad)[::-1].hex().startswith("0000")
+    for t, n in ((int.from_bytes(bytes.fromhex(sub[3]), "little"), h.nonce), (h.time, int.from_bytes(bytes.fromhex(sub[4]), "little"))):
+        bad = oracle.Header(h.version, h.prev_hash, h.merkle_root, t, h.bits, n)
+        assert not oracle.hash_header(bad)[::-1].hex().startswith("0000")
