@@ -227,3 +227,17 @@ def test_work_validation_errors(product):
                    dict(version_mask=0x6000, version_begin=1, version_stride=2, version_count=2),
                    dict(ok, extranonce2_size=1, extranonce2_count=256), dict(ok, extranonce2_size=0, extranonce2_count=1)):
         engine.partition_work(miner.Work(**fields), 0, 1)
+
+
+def test_public_difficulty_example(product, oracle):
+    """The Bitcoin wiki's worked example for compact targets: nBits 0x1b0404cb <-> difficulty 16307.420938523983
+    (public knowledge, not a reference vector; both directions, oracle and C ABI)."""
+    from otedama_b200 import miner
+    d = 16307.420938523983
+    for m in (oracle, miner):
+        t = m.target_from_nbits(0x1B0404CB)
+        assert t[::-1].hex() == "00000000000404cb" + "00" * 24
+        assert int.from_bytes(m.target_from_nbits(0x1D00FFFF), "little") / int.from_bytes(t, "little") == d
+        td = m.target_from_difficulty(d)
+        assert m.nbits_from_target(td) == 0x1B0404CB and td[::-1].hex().startswith("00000000000404cb00000000")
+    assert miner.target_from_difficulty(d) == oracle.target_from_difficulty(d)
