@@ -17,8 +17,8 @@ Two layers:
 Parity: pinned by the reference's own vectors (see tests/test_oracle.py and
 tests/golden/reference_vectors.json); the V1-coinbase and BIP-320 helpers are
 "parity unpinned" (no reference code or test exists for them) — the V1 ones are
-anchored to public data instead, re-derived with hashlib in the tests: block 170
-end to end, and the Stratum V1 documentation's own worked example (subscribe +
+anchored to public data instead, re-derived with hashlib in the tests: blocks 170
+and 100000 end to end, and the Stratum V1 documentation's own worked example (subscribe +
 notify + accepted submit), which fixes the wire conventions.
 """
 from __future__ import annotations

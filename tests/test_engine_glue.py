@@ -220,6 +220,42 @@ def test_stratum_documentation_example_share_is_found_and_submitted(eng, golden)
 
 
 @pytest.mark.gpu
+def test_block_100000_is_found_from_its_notify_form(eng, oracle, golden):
+    """Real chain data with a TWO-level merkle branch and a 2-byte extranonce, at the network target of its
+    time (difficulty 14484): notify form -> K3 (coinbase hash + two folds) / K2 / K1 -> the mined nonce."""
+    engine, miner = eng
+    b = golden["reference_vectors"]["real_world_anchors"]["block100000"]
+    cb = bytes.fromhex(b["coinbase_tx_hex"])
+    tx = [bytes.fromhex(t)[::-1] for t in b["txids_display"]]
+    sp = b["stratum_split"]
+    k, size, e = sp["coinb1_len"], sp["extranonce2_size"], sp["extranonce2_value"]
+    prev = bytes.fromhex(b["prev_hash_display"])[::-1]
+    prev_wire = b"".join(prev[4 * i:4 * i + 4][::-1] for i in range(8)).hex()
+    branch = [tx[1].hex(), oracle.sha256d_hashlib(tx[2] + tx[3]).hex()]
+    params = ["100000", prev_wire, cb[:k].hex(), cb[k + size:].hex(), branch, "%08x" % b["version"], b["bits"],
+              "%08x" % b["time"], True]
+    w = engine.work_from_v1_notify(params, "", size, 0, extranonce2_begin=e - 2, extranonce2_count=4)
+    assert w.target == miner.target_from_nbits(int(b["bits"], 16))          # difficulty 0: the network target
+    w.nonce_begin, w.nonce_count = b["nonce"] - (1 << 20), 1 << 21
+    r = miner.scan(w)
+    assert [(s.extranonce2, s.nonce, s.hash[::-1].hex()) for s in r.shares] == [(e, b["nonce"], b["hash_display"])]
+    assert miner.prepare_instances(w, 2, 1)[0].merkle_root[::-1].hex() == b["merkle_root_display"]
+    assert engine.v1_submit_params(r.shares[0], w)[2:] == ["0602", "%08x" % b["time"], "%08x" % b["nonce"]]
+
+
+@pytest.mark.gpu
+def test_block_125552_nonce_is_found(eng, golden):
+    """The Bitcoin wiki's block-hashing example at its network target (difficulty 244112)."""
+    engine, miner = eng
+    b = golden["reference_vectors"]["real_world_anchors"]["block125552"]
+    h = miner.Header(b["version"], bytes.fromhex(b["prev_hash_display"])[::-1], bytes.fromhex(b["merkle_root_display"])[::-1],
+                     b["time"], int(b["bits"], 16), 0)
+    r = miner.scan(miner.Work(header=h, nbits=h.bits, target=miner.target_from_nbits(h.bits),
+                              nonce_begin=b["nonce"] - (1 << 22), nonce_count=1 << 23))
+    assert [(s.nonce, s.hash[::-1].hex()) for s in r.shares] == [(b["nonce"], b["hash_display"])]
+
+
+@pytest.mark.gpu
 def test_block_1_nonce_is_found(eng, golden):
     engine, miner = eng
     rw = golden["reference_vectors"]["real_world_anchors"]

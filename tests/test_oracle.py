@@ -255,3 +255,33 @@ def test_stratum_documentation_example_pins_the_v1_wire_conventions(oracle, gold
     for t, n in ((int.from_bytes(bytes.fromhex(sub[3]), "little"), h.nonce), (h.time, int.from_bytes(bytes.fromhex(sub[4]), "little"))):
         bad = oracle.Header(h.version, h.prev_hash, h.merkle_root, t, h.bits, n)
         assert not oracle.hash_header(bad)[::-1].hex().startswith("0000")
+
+
+def _hdr_from_anchor(oracle, b, root=None):
+    return oracle.Header(b["version"], bytes.fromhex(b["prev_hash_display"])[::-1],
+                         root if root is not None else bytes.fromhex(b["merkle_root_display"])[::-1], b["time"],
+                         int(b["bits"], 16), b["nonce"])
+
+
+def test_more_real_world_anchors(oracle, golden):
+    """Block 125552 (the Bitcoin wiki's block-hashing example) and block 100000, whose coinbase has a two-level
+    merkle branch and a 2-byte extranonce: coinbase -> txid -> fold twice -> root -> header -> published hash."""
+    rw = _rw(golden)
+    b = rw["block125552"]
+    hh = oracle.hash_header(_hdr_from_anchor(oracle, b))
+    assert hh[::-1].hex() == b["hash_display"] and oracle.meets_target(hh, int(b["bits"], 16))
+    b = rw["block100000"]
+    cb = bytes.fromhex(b["coinbase_tx_hex"])
+    tx = [bytes.fromhex(t)[::-1] for t in b["txids_display"]]
+    assert oracle.sha256d_hashlib(cb) == tx[0]
+    sp = b["stratum_split"]
+    k, size = sp["coinb1_len"], sp["extranonce2_size"]
+    en2 = oracle.extranonce2_bytes(sp["extranonce2_value"], size)
+    assert cb[k:k + size] == en2
+    branch = [tx[1], oracle.sha256d_hashlib(tx[2] + tx[3])]
+    root = oracle.v1_merkle_root(cb[:k], b"", en2, cb[k + size:], branch)
+    assert root[::-1].hex() == b["merkle_root_display"] == oracle.v1_merkle_root_py(cb[:k], b"", en2, cb[k + size:], branch)[::-1].hex()
+    # the branch order matters: swapped levels give another root
+    assert oracle.v1_merkle_root(cb[:k], b"", en2, cb[k + size:], branch[::-1]) != root
+    hh = oracle.hash_header(_hdr_from_anchor(oracle, b, root))
+    assert hh[::-1].hex() == b["hash_display"] and oracle.meets_target(hh, int(b["bits"], 16))
