@@ -61,6 +61,35 @@ int main(int argc, char** argv)
     CHECK(w.job_id == 42 && w.header.version == 0x20000004u && memcmp(w.target, target, 32) == 0 && w.nonce_count == 0);
     CHECK(otd_work_from_v1_job("not-a-number", 1, zero, 1, 0x1d00ffffu, 0.0, &w) == OTD_EINVAL);
 
+    /* the Stratum documentation's example, from plain C: notify -> work unit, share -> submit fields */
+    {
+        otd_v1_notify_t nt;
+        memset(&nt, 0, sizeof nt);
+        nt.job_id = "191";
+        nt.prevhash_hex = "4d16b6f85af6e2198f44ae2a6de67f78487ae5611b77c6c0440b921e00000000";
+        nt.coinb1_hex = "01000000010000000000000000000000000000000000000000000000000000000000000000ffffffff20020862062f503253482f04b8864e5008";
+        nt.coinb2_hex = "072f736c7573682f000000000100f2052a010000001976a914d23fcdf86f7e756a64a7a9688ef9903327048ed988ac00000000";
+        nt.version_hex = "00000002";
+        nt.nbits_hex = "1c2ac4af";
+        nt.ntime_hex = "504e86b9";
+        uint8_t scratch[256];
+        size_t need = 0;
+        otd_work_t vw;
+        CHECK(otd_work_from_v1_notify(&nt, "08000002", 4, 1.0, 0, &vw, scratch, 8, &need) == OTD_ERANGE && need > 8 && need <= sizeof scratch);
+        CHECK(otd_work_from_v1_notify(&nt, "08000002", 4, 1.0, 0, &vw, scratch, sizeof scratch, &need) == OTD_OK);
+        CHECK(vw.job_id == 191 && vw.header.version == 2 && vw.header.bits == 0x1c2ac4afu && vw.header.time == 0x504e86b9u);
+        CHECK(vw.header.prev_hash[0] == 0xf8 && vw.header.prev_hash[3] == 0x4d && vw.header.prev_hash[31] == 0x00);
+        CHECK(vw.coinb1_len == 58 && vw.extranonce1_len == 4 && vw.extranonce1[0] == 0x08 && vw.extranonce2_size == 4 && vw.n_branches == 0);
+        otd_share_t sh;
+        memset(&sh, 0, sizeof sh);
+        sh.job_id = 191; sh.ntime = 0x504e86edu; sh.nonce = 0xb2957c02u; sh.version = 2; sh.extranonce2 = 0x01000000u;
+        otd_v1_submit_t sub;
+        CHECK(otd_share_to_v1_submit(&sh, vw.extranonce2_size, 0, &sub) == OTD_OK);
+        CHECK(strcmp(sub.extranonce2_hex, "00000001") == 0 && strcmp(sub.ntime_hex, "504e86ed") == 0 &&
+              strcmp(sub.nonce_hex, "b2957c02") == 0 && sub.version_bits_hex[0] == 0);
+        CHECK(otd_share_to_v1_submit(&sh, 17, 0, &sub) == OTD_EINVAL);
+    }
+
     const int ndev = otd_device_count();
     CHECK(ndev >= 0);
     memset(&w, 0, sizeof w);
