@@ -9,7 +9,7 @@
 
 Every share that comes back is re-hashed by the CPU oracle (soundness, bit-exact).  The full spaces
 (2^48 candidates) are far beyond a test run, so each config runs for --seconds and reports the rate.
-    python scripts/run_configs.py --gpus 1 --seconds 20
+    python tests/full_size/run_configs.py --gpus 1 --seconds 20
 """
 import argparse
 import json
@@ -17,7 +17,7 @@ import os
 import sys
 import time
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from otedama_b200 import capi, miner, workloads as W  # noqa: E402
 from oracle import oracle as o  # noqa: E402  (checker only)

@@ -6,7 +6,7 @@ process, for --seconds; every --interval seconds it logs, per GPU, the hash rate
 (from otd_worker_stats) and power / SM clock / temperature (otd_device_telemetry = NVML), plus the
 joules-per-terahash the reference's efficiency gauge would show (engine/metrics.go:488).  Every share
 is re-hashed by the CPU oracle at the end.
-    python scripts/sustained.py --gpus 1 --seconds 600 --interval 10 --out gpurun_out/sustained_1gpu.csv
+    python tests/full_size/sustained.py --gpus 1 --seconds 600 --interval 10 --out gpurun_out/sustained_1gpu.csv
 """
 import argparse
 import json
@@ -14,7 +14,7 @@ import os
 import sys
 import time
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from otedama_b200 import capi, hal, miner, workloads as W  # noqa: E402
 from oracle import oracle as o  # noqa: E402  (checker only)
