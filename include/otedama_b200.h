@@ -106,6 +106,8 @@ int otd_hash_headers(int device_index, const uint8_t* headers80, size_t n, uint8
  * one header, nonce-only search of all 2^32 nonces. */
 #define OTD_WORK_REPEAT 1u /* when the space is exhausted start over (the reference's
                               uint32 wrap, worker.go:279) instead of going idle */
+#define OTD_WORK_PER_VERSION_LAUNCH 2u /* rolled versions: one plain scan launch per version
+                              instance instead of the version-shared kernel (A/B checks) */
 
 typedef struct {
     uint32_t job_id;      /* Work.JobID     */
@@ -343,6 +345,20 @@ int otd_scan_noalloc(int device_index, const otd_work_t* work, int kernel_varian
  * names[i] (each up to 32 bytes incl. NUL) when names != NULL. */
 int otd_scan_variants(char (*names)[32], int max_names);
 int otd_scan_default_variant(void);
+
+/* Version-shared scan variants.  A work that rolls BIP-320 version bits
+ * (version_mask != 0, at least two version instances in the slice) is searched by
+ * a second kernel family: the versions of a job differ only in block 1 of the
+ * header, so block 2's message schedule is expanded once per nonce and reused by
+ * up to 16 version instances per launch (csrc/scan_vs_kernel.cuh).  No reference
+ * counterpart: the reference ignores version rolling
+ * (internal/poolproto/stratumv1/stratumv1.go:280-281).  The share set is the same
+ * as with one plain launch per version (OTD_WORK_PER_VERSION_LAUNCH).
+ * otd_vs_select picks the variant every later run of this process uses for rolled
+ * work: an index, -1 = library default, -2 = never share (plain kernel per version). */
+int otd_vs_variants(char (*names)[32], int max_names);
+int otd_vs_default_variant(void);
+int otd_vs_select(int variant);
 
 /* Job-preparation kernels exposed for parity tests (K3: extranonce2 roll +
  * coinbase hash + merkle fold; K2: rolled version). Fills n merkle roots

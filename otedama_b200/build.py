@@ -20,10 +20,11 @@ CSRC = os.path.join(_PKG, "csrc")
 OBJ = os.path.join(CSRC, "_obj")
 LIB_PATH = os.path.join(_PKG, "libotedama_b200.so")
 HEADERS = [os.path.join(CSRC, f) for f in ("sha256_core.cuh", "scan_core.cuh", "scan_kernel.cuh", "job_kernels.cuh",
-                                           "intpeak.cuh", "scan_variants.h")] + \
+                                           "intpeak.cuh", "scan_variants.h", "scan_vs_core.cuh", "scan_vs_kernel.cuh")] + \
     [os.path.join(_ROOT, "include", "otedama_b200.h")]
 MAIN_SRC = os.path.join(CSRC, "otedama_b200.cu")
 VARIANT_SRC = os.path.join(CSRC, "scan_variant.cu")
+VS_VARIANT_SRC = os.path.join(CSRC, "scan_vs_variant.cu")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -36,6 +37,11 @@ NVCC_FLAGS = [
 def variant_indices() -> list:
     txt = open(os.path.join(CSRC, "scan_variants.h")).read()
     return [int(m) for m in re.findall(r"^\s*X\((\d+),", txt, flags=re.M)]
+
+
+def vs_variant_indices() -> list:
+    txt = open(os.path.join(CSRC, "scan_variants.h")).read()
+    return [int(m) for m in re.findall(r"^\s*Y\((\d+),", txt, flags=re.M)]
 
 
 def _digest(paths, extra="") -> str:
@@ -59,7 +65,7 @@ STAMP_PATH = LIB_PATH + ".srchash"
 
 
 def source_hash() -> str:
-    return _digest(HEADERS + [MAIN_SRC, VARIANT_SRC], " ".join(NVCC_FLAGS))
+    return _digest(HEADERS + [MAIN_SRC, VARIANT_SRC, VS_VARIANT_SRC], " ".join(NVCC_FLAGS))
 
 
 def needs_build() -> bool:
@@ -80,6 +86,9 @@ def build(force: bool = False, verbose: bool = False, jobs: int = 0) -> str:
     key_var = _digest(HEADERS[:3] + [HEADERS[5], VARIANT_SRC], " ".join(NVCC_FLAGS))
     for i in variant_indices():
         tasks.append((VARIANT_SRC, os.path.join(OBJ, f"variant{i}_{key_var}.o"), [f"-DOTD_VIDX={i}"]))
+    key_vs = _digest(HEADERS[:3] + HEADERS[5:8] + [VS_VARIANT_SRC], " ".join(NVCC_FLAGS))
+    for i in vs_variant_indices():
+        tasks.append((VS_VARIANT_SRC, os.path.join(OBJ, f"vsvariant{i}_{key_vs}.o"), [f"-DOTD_VSIDX={i}"]))
     todo = [t for t in tasks if force or not os.path.exists(t[1])]
     jobs = jobs or min(len(todo) or 1, os.cpu_count() or 1)
     with cf.ThreadPoolExecutor(max_workers=jobs) as ex:

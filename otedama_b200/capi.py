@@ -18,6 +18,7 @@ HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "otedama_b200.h")
 
 OTD_OK, OTD_EINVAL, OTD_ENODEV, OTD_ENOMEM, OTD_EBUSY, OTD_ECUDA, OTD_ERANGE = 0, -22, -19, -12, -16, -5, -34
 OTD_WORK_REPEAT = 1
+OTD_WORK_PER_VERSION_LAUNCH = 2
 OTD_NOALLOC_MAX_SHARES = 4096
 
 
@@ -127,6 +128,9 @@ _SIGS = {
                                  POINTER(c_uint64)]),
     "otd_scan_variants": (c_int, [c_void_p, c_int]),
     "otd_scan_default_variant": (c_int, []),
+    "otd_vs_variants": (c_int, [c_void_p, c_int]),
+    "otd_vs_default_variant": (c_int, []),
+    "otd_vs_select": (c_int, [c_int]),
     "otd_prepare_instances": (c_int, [c_int, POINTER(CWork), c_uint32, c_uint32, c_char_p,
                                       POINTER(c_uint32), POINTER(c_uint64), c_char_p]),
     "otd_int_peak": (c_int, [c_int, c_int, c_int, POINTER(c_double), POINTER(c_double), POINTER(c_double)]),

@@ -31,6 +31,7 @@
 #include "job_kernels.cuh"
 #include "scan_kernel.cuh"
 #include "scan_variants.h"
+#include "scan_vs_kernel.cuh"
 
 using namespace otd;
 
@@ -549,6 +550,39 @@ extern "C" int otd_scan_variants(char (*names)[32], int max_names)
 }
 extern "C" int otd_scan_default_variant(void) { return kDefaultVariant; }
 
+// Version-shared variants (scan_vs_kernel.cuh): used when a work rolls BIP-320 version bits.
+struct VsVariant {
+    const char* name;
+    int iter, block;
+    otd_vs_launch_fn fn;
+};
+#define OTD_VS_ROW(idx, name, iter, kn, minb, block) {name, iter, block, otd_vs_launch_##idx},
+static const VsVariant kVsVariants[] = {OTD_VS_VARIANTS(OTD_VS_ROW)};
+#undef OTD_VS_ROW
+static const int kNumVsVariants = (int)(sizeof kVsVariants / sizeof kVsVariants[0]);
+static std::atomic<int> g_vs_choice{-1};  // -1 library default, -2 off, >= 0 a variant index
+
+extern "C" int otd_vs_variants(char (*names)[32], int max_names)
+{
+    if (names)
+        for (int i = 0; i < kNumVsVariants && i < max_names; i++) snprintf(names[i], 32, "%s", kVsVariants[i].name);
+    return kNumVsVariants;
+}
+extern "C" int otd_vs_default_variant(void) { return OTD_DEFAULT_VS_VARIANT; }
+extern "C" int otd_vs_select(int variant)
+{
+    if (variant < -2 || variant >= kNumVsVariants) return fail(OTD_EINVAL, "otd_vs_select: unknown variant");
+    g_vs_choice.store(variant);
+    return OTD_OK;
+}
+// the variant a run uses for rolled work, or nullptr when sharing is switched off
+static const VsVariant* vs_variant_in_use()
+{
+    const int c = g_vs_choice.load();
+    if (c == -2) return nullptr;
+    return &kVsVariants[c < 0 ? OTD_DEFAULT_VS_VARIANT : c];
+}
+
 // -------------------------------------------------------------- work copy --
 struct WorkCopy {
     otd_work_t w;
@@ -661,7 +695,7 @@ extern "C" int otd_share_to_v1_submit(const otd_share_t* share, uint32_t extrano
 
 // ------------------------------------------------------------------ engine --
 struct RunStats {
-    uint64_t hashes = 0, launches = 0, candidates = 0, found = 0, ring_dropped = 0;
+    uint64_t hashes = 0, launches = 0, candidates = 0, found = 0, ring_dropped = 0, shared_launches = 0;
     double kernel_ms = 0, span_ms = 0;
 };
 
@@ -678,8 +712,10 @@ struct Slot {
     RingEntry* h_ent = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr, edone = nullptr;
     bool busy = false;
-    uint64_t count = 0, en2 = 0, tile = 0;
-    uint32_t version = 0;
+    uint64_t count = 0, en2 = 0, tile = 0;  // candidates of the launch, extranonce2 value, candidates per block
+    uint32_t inst0 = 0;                     // instance index (low 32 bits) of the launch's first version instance
+    uint32_t n_ver = 1;                     // version instances in the launch (1 for the plain kernel)
+    uint32_t versions[kVsMaxVersions] = {0};
 };
 
 class Engine {
@@ -878,7 +914,9 @@ class Engine {
             sh.job_id = wc.w.job_id;
             sh.nonce = s.h_ent[i].nonce;
             sh.ntime = wc.w.header.time;
-            sh.version = s.version;
+            const uint32_t vi = s.h_ent[i].instance - s.inst0;  // which of the launch's version instances
+            if (vi >= s.n_ver) return fail(OTD_ECUDA, "scan kernel: ring entry names an instance outside its launch");
+            sh.version = s.versions[vi];
             memcpy(sh.hash, s.h_ent[i].hash, 32);
             sh.extranonce2 = s.en2;
             sh.work_seq = seq;
@@ -896,6 +934,7 @@ class Engine {
         if (!ready) return fail(OTD_EINVAL, "engine not initialised");
         if (variant < 0 || variant >= num_usable_variants()) variant = kDefaultVariant;
         const ScanVariant& kv = kVariants[variant];
+        const VsVariant* const vs = (wc.w.flags & OTD_WORK_PER_VERSION_LAUNCH) ? nullptr : vs_variant_in_use();
         if (launch_log2 == 0) launch_log2 = 32;
         launch_log2 = std::min(32u, std::max(16u, launch_log2));
         const uint64_t chunk = 1ull << launch_log2;
@@ -920,31 +959,49 @@ class Engine {
                 if (s.busy && (rc = harvest(s, wc, seq, sink, rs, aborted, abort_sent))) return rc;
             if (abort_sent || aborted()) break;
             if ((rc = prepare_batch(wc, bf, nb, nullptr))) return rc;
-            for (uint32_t i = 0; i < nb && !abort_sent && !halted; i++) {
+            for (uint32_t i = 0; i < nb && !abort_sent && !halted;) {
                 const uint64_t inst = bf + i;
                 const uint64_t en2 = wc.w.extranonce2_begin + (inst / wc.n_ver) * wc.en2_stride;
-                for (uint64_t off = 0; off < wc.nonce_count; off += chunk) {
+                // Version instances of one extranonce2 value share block 2 of hash 1: up to kVsMaxVersions of
+                // them go into ONE version-shared launch (scan_vs_kernel.cuh); a lone instance takes the plain kernel.
+                uint32_t grp = 1;
+                if (vs && wc.w.version_mask)
+                    grp = (uint32_t)std::min<uint64_t>({(uint64_t)kVsMaxVersions, wc.n_ver - inst % wc.n_ver, (uint64_t)(nb - i)});
+                const bool shared = grp >= 2;
+                const uint64_t blk_nonces = shared ? (uint64_t)vs->block * vs->iter : (uint64_t)kv.block * kv.v * kv.iter;
+                // nonces per launch: the configured candidate count split over the group, in whole blocks
+                const uint64_t step = shared ? std::max(blk_nonces, chunk / grp / blk_nonces * blk_nonces) : chunk;
+                VsParams vp;
+                if (shared) memcpy(vp.jc, &h_consts[i], sizeof(JobConsts) * grp);
+                for (uint64_t off = 0; off < wc.nonce_count; off += step) {
                     Slot& s = slot[next];
                     next ^= 1;
                     if (s.busy && (rc = harvest(s, wc, seq, sink, rs, aborted, abort_sent))) return rc;
                     if (abort_sent || aborted()) { halted = true; break; }
-                    const uint64_t cnt = std::min(chunk, wc.nonce_count - off);
+                    const uint64_t cnt = std::min(step, wc.nonce_count - off);
                     CU_TRY(cudaMemsetAsync(s.d_hdr, 0, sizeof(RingHeader), stream));
                     if (first_launch) { CU_TRY(cudaEventRecord(ev_first, stream)); first_launch = false; }
                     CU_TRY(cudaEventRecord(s.e0, stream));
-                    cudaError_t le = kv.fn(h_consts[i], wc.w.nonce_begin + (uint32_t)off, cnt, (uint32_t)(inst & 0xffffffffu),
-                                           s.d_hdr, s.d_ent, cap, d_stop, gen, stream);
+                    cudaError_t le = shared
+                        ? vs->fn(vp, grp, wc.w.nonce_begin + (uint32_t)off, cnt, (uint32_t)(inst & 0xffffffffu), s.d_hdr,
+                                 s.d_ent, cap, d_stop, gen, stream)
+                        : kv.fn(h_consts[i], wc.w.nonce_begin + (uint32_t)off, cnt, (uint32_t)(inst & 0xffffffffu),
+                                s.d_hdr, s.d_ent, cap, d_stop, gen, stream);
                     if (le != cudaSuccess) return fail(OTD_ECUDA, std::string("scan launch: ") + cudaGetErrorString(le));
                     CU_TRY(cudaEventRecord(s.e1, stream));
                     CU_TRY(cudaEventRecord(ev_last, stream));
                     CU_TRY(cudaMemcpyAsync(s.h_hdr, s.d_hdr, sizeof(RingHeader), cudaMemcpyDeviceToHost, stream));
                     CU_TRY(cudaEventRecord(s.edone, stream));
                     s.busy = true;
-                    s.count = cnt;
-                    s.tile = (uint64_t)kv.block * kv.v * kv.iter;
+                    s.count = cnt * grp;
+                    s.tile = blk_nonces * grp;
                     s.en2 = wc.has_coinbase ? en2 : 0;
-                    s.version = h_versions[i];
+                    s.inst0 = (uint32_t)(inst & 0xffffffffu);
+                    s.n_ver = grp;
+                    for (uint32_t k = 0; k < grp; k++) s.versions[k] = h_versions[i + k];
+                    if (shared) rs.shared_launches += 1;
                 }
+                i += grp;
             }
         }
         for (int k = 0; k < 2; k++) {

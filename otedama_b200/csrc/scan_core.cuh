@@ -375,6 +375,74 @@ template <int V, unsigned KN> OTD_HD vw<V> cadd(const Ops<KN>&, const vw<V>& a, 
     rnd(op, c, d, e, f, g, h, a, b, w[(R) + 6], Kc((R) + 6));   \
     rnd(op, b, c, d, e, f, g, h, a, w[(R) + 7], Kc((R) + 7));
 
+// Hash 2 of SHA-256d up to e after round 60, from the eight digest words of hash 1
+// (big-endian state words, midstate already added).  Digest word 7 of the double
+// hash = IV7 + result.  Shared by the plain scan (scan_core) and the version-shared
+// scan (scan_vs_core.cuh).
+template <int V, unsigned KN>
+OTD_HD vw<V> hash2_e60(const Ops<KN>& op, const vw<V>& x0, const vw<V>& x1, const vw<V>& x2, const vw<V>& x3,
+                       const vw<V>& x4, const vw<V>& x5, const vw<V>& x6, const vw<V>& x7)
+{
+    // message = digest of hash 1, padding, length 256 bits
+    vw<V> w[64];
+    vw<V> a, b, c, d, e, f, g, h;
+    w[0] = x0; w[1] = x1; w[2] = x2; w[3] = x3; w[4] = x4; w[5] = x5; w[6] = x6; w[7] = x7;
+    // W8 = 0x80000000, W9..14 = 0, W15 = 0x100: written out so the zero terms vanish
+    w[16] = padd(op, vs0(op, w[1]), w[0]);
+    w[17] = padd(op, vs0(op, w[2]), w[1]) + ssig1(0x100u);
+    w[18] = padd(op, padd(op, vs1(op, w[16]), vs0(op, w[3])), w[2]);
+    w[19] = padd(op, padd(op, vs1(op, w[17]), vs0(op, w[4])), w[3]);
+    w[20] = padd(op, padd(op, vs1(op, w[18]), vs0(op, w[5])), w[4]);
+    w[21] = padd(op, padd(op, vs1(op, w[19]), vs0(op, w[6])), w[5]);
+    w[22] = sched(op, w[20], bc<V>(0x100u), w[7], w[6]);
+    w[23] = padd(op, padd(op, vs1(op, w[21]), w[16]), w[7]) + ssig0(0x80000000u);
+    w[24] = padd(op, vs1(op, w[22]), w[17]) + 0x80000000u;
+    w[25] = padd(op, vs1(op, w[23]), w[18]);
+    w[26] = padd(op, vs1(op, w[24]), w[19]);
+    w[27] = padd(op, vs1(op, w[25]), w[20]);
+    w[28] = padd(op, vs1(op, w[26]), w[21]);
+    w[29] = padd(op, vs1(op, w[27]), w[22]);
+    w[30] = padd(op, vs1(op, w[28]), w[23]) + ssig0(0x100u);
+    w[31] = padd(op, padd(op, vs1(op, w[29]), w[24]), vs0(op, w[16])) + 0x100u;
+#pragma unroll
+    for (int i = 32; i < 61; i++) w[i] = sched(op, w[i - 2], w[i - 7], w[i - 15], w[i - 16]);
+
+    a = bc<V>(IV0); b = bc<V>(IV1); c = bc<V>(IV2); d = bc<V>(IV3);
+    e = bc<V>(IV4); f = bc<V>(IV5); g = bc<V>(IV6); h = bc<V>(IV7);
+    // rounds 0..3 still see compile-time constants (IV words) in the state: plain C so they fold
+    {
+        const Ops<0> fold{};
+        rnd(fold, a, b, c, d, e, f, g, h, w[0], Kc(0));
+        rnd(fold, h, a, b, c, d, e, f, g, w[1], Kc(1));
+        rnd(fold, g, h, a, b, c, d, e, f, w[2], Kc(2));
+        rnd(fold, f, g, h, a, b, c, d, e, w[3], Kc(3));
+    }
+    rnd(op, e, f, g, h, a, b, c, d, w[4], Kc(4));
+    rnd(op, d, e, f, g, h, a, b, c, w[5], Kc(5));
+    rnd(op, c, d, e, f, g, h, a, b, w[6], Kc(6));
+    rnd(op, b, c, d, e, f, g, h, a, w[7], Kc(7));
+    rnd(op, a, b, c, d, e, f, g, h, Kc(8) + 0x80000000u);
+    rnd(op, h, a, b, c, d, e, f, g, Kc(9));
+    rnd(op, g, h, a, b, c, d, e, f, Kc(10));
+    rnd(op, f, g, h, a, b, c, d, e, Kc(11));
+    rnd(op, e, f, g, h, a, b, c, d, Kc(12));
+    rnd(op, d, e, f, g, h, a, b, c, Kc(13));
+    rnd(op, c, d, e, f, g, h, a, b, Kc(14));
+    rnd(op, b, c, d, e, f, g, h, a, Kc(15) + 0x100u);
+    OTD_R8(16, a, b, c, d, e, f, g, h)
+    OTD_R8(24, a, b, c, d, e, f, g, h)
+    OTD_R8(32, a, b, c, d, e, f, g, h)
+    OTD_R8(40, a, b, c, d, e, f, g, h)
+    OTD_R8(48, a, b, c, d, e, f, g, h)
+    // round 56 full, rounds 57..60 e-chain only
+    rnd(op, a, b, c, d, e, f, g, h, w[56], Kc(56));
+    rnd_e(op, c, d, e, f, g, w[57], Kc(57));
+    rnd_e(op, b, c, d, e, f, w[58], Kc(58));
+    rnd_e(op, a, b, c, d, e, w[59], Kc(59));
+    rnd_e(op, h, a, b, c, d, w[60], Kc(60));
+    return h;
+}
+
 // Returns e after round 60 of the second hash for V candidates whose block-2
 // word 3 (the big-endian nonce word) is w3.  Digest word 7 = IV7 + result.
 // HALF (performance experiments only, never shipped as a scan variant's result):
@@ -462,63 +530,10 @@ OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
     if (HALF) return g + (jc.mid[7] - IV7);
 
     // ---------------- hash 2 ----------------
-    // message = digest of hash 1 (state + midstate), padding, length 256 bits
-    w[0] = cadd(op, h, jc.mid[0]); w[1] = cadd(op, a, jc.mid[1]); w[2] = cadd(op, b, jc.mid[2]); w[3] = cadd(op, c, jc.mid[3]);
-    w[4] = cadd(op, d, jc.mid[4]); w[5] = cadd(op, e, jc.mid[5]); w[6] = cadd(op, f, jc.mid[6]); w[7] = cadd(op, g, jc.mid[7]);
-    // W8 = 0x80000000, W9..14 = 0, W15 = 0x100: written out so the zero terms vanish
-    w[16] = padd(op, vs0(op, w[1]), w[0]);
-    w[17] = padd(op, vs0(op, w[2]), w[1]) + ssig1(0x100u);
-    w[18] = padd(op, padd(op, vs1(op, w[16]), vs0(op, w[3])), w[2]);
-    w[19] = padd(op, padd(op, vs1(op, w[17]), vs0(op, w[4])), w[3]);
-    w[20] = padd(op, padd(op, vs1(op, w[18]), vs0(op, w[5])), w[4]);
-    w[21] = padd(op, padd(op, vs1(op, w[19]), vs0(op, w[6])), w[5]);
-    w[22] = sched(op, w[20], bc<V>(0x100u), w[7], w[6]);
-    w[23] = padd(op, padd(op, vs1(op, w[21]), w[16]), w[7]) + ssig0(0x80000000u);
-    w[24] = padd(op, vs1(op, w[22]), w[17]) + 0x80000000u;
-    w[25] = padd(op, vs1(op, w[23]), w[18]);
-    w[26] = padd(op, vs1(op, w[24]), w[19]);
-    w[27] = padd(op, vs1(op, w[25]), w[20]);
-    w[28] = padd(op, vs1(op, w[26]), w[21]);
-    w[29] = padd(op, vs1(op, w[27]), w[22]);
-    w[30] = padd(op, vs1(op, w[28]), w[23]) + ssig0(0x100u);
-    w[31] = padd(op, padd(op, vs1(op, w[29]), w[24]), vs0(op, w[16])) + 0x100u;
-#pragma unroll
-    for (int i = 32; i < 61; i++) w[i] = sched(op, w[i - 2], w[i - 7], w[i - 15], w[i - 16]);
-
-    a = bc<V>(IV0); b = bc<V>(IV1); c = bc<V>(IV2); d = bc<V>(IV3);
-    e = bc<V>(IV4); f = bc<V>(IV5); g = bc<V>(IV6); h = bc<V>(IV7);
-    // rounds 0..3 still see compile-time constants (IV words) in the state: plain C so they fold
-    {
-        const Ops<0> fold{};
-        rnd(fold, a, b, c, d, e, f, g, h, w[0], Kc(0));
-        rnd(fold, h, a, b, c, d, e, f, g, w[1], Kc(1));
-        rnd(fold, g, h, a, b, c, d, e, f, w[2], Kc(2));
-        rnd(fold, f, g, h, a, b, c, d, e, w[3], Kc(3));
-    }
-    rnd(op, e, f, g, h, a, b, c, d, w[4], Kc(4));
-    rnd(op, d, e, f, g, h, a, b, c, w[5], Kc(5));
-    rnd(op, c, d, e, f, g, h, a, b, w[6], Kc(6));
-    rnd(op, b, c, d, e, f, g, h, a, w[7], Kc(7));
-    rnd(op, a, b, c, d, e, f, g, h, Kc(8) + 0x80000000u);
-    rnd(op, h, a, b, c, d, e, f, g, Kc(9));
-    rnd(op, g, h, a, b, c, d, e, f, Kc(10));
-    rnd(op, f, g, h, a, b, c, d, e, Kc(11));
-    rnd(op, e, f, g, h, a, b, c, d, Kc(12));
-    rnd(op, d, e, f, g, h, a, b, c, Kc(13));
-    rnd(op, c, d, e, f, g, h, a, b, Kc(14));
-    rnd(op, b, c, d, e, f, g, h, a, Kc(15) + 0x100u);
-    OTD_R8(16, a, b, c, d, e, f, g, h)
-    OTD_R8(24, a, b, c, d, e, f, g, h)
-    OTD_R8(32, a, b, c, d, e, f, g, h)
-    OTD_R8(40, a, b, c, d, e, f, g, h)
-    OTD_R8(48, a, b, c, d, e, f, g, h)
-    // round 56 full, rounds 57..60 e-chain only
-    rnd(op, a, b, c, d, e, f, g, h, w[56], Kc(56));
-    rnd_e(op, c, d, e, f, g, w[57], Kc(57));
-    rnd_e(op, b, c, d, e, f, w[58], Kc(58));
-    rnd_e(op, a, b, c, d, e, w[59], Kc(59));
-    rnd_e(op, h, a, b, c, d, w[60], Kc(60));
-    return h;
+    // message = digest of hash 1 (state + midstate)
+    return hash2_e60<V, KN>(op, cadd(op, h, jc.mid[0]), cadd(op, a, jc.mid[1]), cadd(op, b, jc.mid[2]),
+                            cadd(op, c, jc.mid[3]), cadd(op, d, jc.mid[4]), cadd(op, e, jc.mid[5]),
+                            cadd(op, f, jc.mid[6]), cadd(op, g, jc.mid[7]));
 }
 
 // ---------------------------------------------------------------------------

@@ -11,6 +11,7 @@
 namespace otd {
 struct RingHeader;
 struct RingEntry;
+struct VsParams;
 }  // namespace otd
 
 // index, name, V, ITER, knobs, HALF, MINB, BLOCK.  Production variants first (indices below
@@ -39,6 +40,19 @@ struct RingEntry;
 #define OTD_NUM_PRODUCTION_VARIANTS 6
 #define OTD_DEFAULT_VARIANT 0
 
+// Version-shared scan variants (scan_vs_kernel.cuh): index, name, ITER, knobs, MINB, BLOCK.  All of them compute
+// the full SHA-256d.  OTD_KN_VS(n, m): the shipped add placement with n/8 of the immediate-constant rounds and
+// m/8 of the shared-schedule rounds built from IMADs only (m = 0 reads as 8/8).
+#define OTD_KN_VS(n, m) (OTD_KN_ADDS | otd::KN_SP | otd::KN_T1Z | OTD_KN_Z_EIGHTHS(n) | OTD_KN_VSZ_EIGHTHS(m))
+#define OTD_VS_VARIANTS(Y)                                  \
+    Y(0, "vs_z6_r6_b4", 4, OTD_KN_VS(6, 6), 4, 256)         \
+    Y(1, "vs_z6_r8_b4", 4, OTD_KN_VS(6, 0), 4, 256)         \
+    Y(2, "vs_z6_r4_b4", 4, OTD_KN_VS(6, 4), 4, 256)         \
+    Y(3, "vs_z6_r7_b4", 4, OTD_KN_VS(6, 7), 4, 256)         \
+    Y(4, "vs_z5_r6_b4", 4, OTD_KN_VS(5, 6), 4, 256)         \
+    Y(5, "vs_z7_r7_b4", 4, OTD_KN_VS(7, 7), 4, 256)
+#define OTD_DEFAULT_VS_VARIANT 0
+
 typedef cudaError_t (*otd_scan_launch_fn)(const otd::JobConsts&, uint32_t nonce_begin,
                                           unsigned long long count, uint32_t instance,
                                           otd::RingHeader*, otd::RingEntry*, uint32_t cap,
@@ -50,3 +64,15 @@ typedef cudaError_t (*otd_scan_launch_fn)(const otd::JobConsts&, uint32_t nonce_
                                       unsigned int, cudaStream_t);
 OTD_SCAN_VARIANTS(OTD_DECLARE_VARIANT)
 #undef OTD_DECLARE_VARIANT
+
+// Version-shared launch: n_ver instances (p.jc[0..n_ver)) x the nonce window, instance index of p.jc[0] = instance0.
+typedef cudaError_t (*otd_vs_launch_fn)(const otd::VsParams&, uint32_t n_ver, uint32_t nonce_begin,
+                                        unsigned long long count, uint32_t instance0, otd::RingHeader*,
+                                        otd::RingEntry*, uint32_t cap, const unsigned int* stop, unsigned int gen,
+                                        cudaStream_t);
+#define OTD_DECLARE_VS_VARIANT(idx, name, iter, kn, minb, block)                                              \
+    cudaError_t otd_vs_launch_##idx(const otd::VsParams&, uint32_t, uint32_t, unsigned long long, uint32_t, \
+                                    otd::RingHeader*, otd::RingEntry*, uint32_t, const unsigned int*,       \
+                                    unsigned int, cudaStream_t);
+OTD_VS_VARIANTS(OTD_DECLARE_VS_VARIANT)
+#undef OTD_DECLARE_VS_VARIANT

@@ -127,6 +127,7 @@ class Work:
     target: bytes = b"\x00" * 32
     # search-space extension (defaults = the reference's nonce-only search)
     repeat: bool = False
+    per_version_launch: bool = False   # rolled versions: plain kernel per version instead of the version-shared one
     nonce_begin: int = 0
     nonce_count: int = 0            # 0 = 2^32
     version_mask: int = 0
@@ -150,7 +151,8 @@ class Work:
         w.job_id, w.channel_id, w.nbits = self.job_id & 0xFFFFFFFF, self.channel_id & 0xFFFFFFFF, self.nbits & 0xFFFFFFFF
         w.header = self.header._c()
         w.target[:] = self.target
-        w.flags = capi.OTD_WORK_REPEAT if self.repeat else 0
+        w.flags = (capi.OTD_WORK_REPEAT if self.repeat else 0) | \
+                  (capi.OTD_WORK_PER_VERSION_LAUNCH if self.per_version_launch else 0)
         w.nonce_begin, w.nonce_count = self.nonce_begin, self.nonce_count
         w.version_mask, w.version_begin = self.version_mask, self.version_begin
         w.version_count, w.version_stride = self.version_count, self.version_stride
@@ -258,6 +260,20 @@ def scan_variants() -> List[str]:
 
 def default_variant() -> int:
     return int(lib().otd_scan_default_variant())
+
+
+def vs_variants() -> List[str]:
+    """Version-shared scan variants (used for work that rolls BIP-320 version bits)."""
+    return capi.names_list(lib().otd_vs_variants)
+
+
+def default_vs_variant() -> int:
+    return int(lib().otd_vs_default_variant())
+
+
+def vs_select(variant: int) -> None:
+    """Variant for rolled work from now on: index, -1 = library default, -2 = never share."""
+    check(lib().otd_vs_select(variant))
 
 
 # ----------------------------------------------------------------------------

@@ -3,6 +3,7 @@
 // can be checked on a CPU-only box (tests/test_fold_host.py).
 // Test helper only — not shipped, not a fallback.
 #include "../../otedama_b200/csrc/scan_core.cuh"
+#include "../../otedama_b200/csrc/scan_vs_core.cuh"
 using namespace otd;
 
 template <int V, unsigned KN>
@@ -38,7 +39,49 @@ static void consts_for(const uint8_t hdr76[76], const uint8_t target[32], JobCon
     fold_job_consts(mid, tail[0], tail[1], tail[2], tgt, jc);
 }
 
+// Version-shared core: the schedule of block 2 expanded once (from instance 0's constants),
+// then one state recurrence + hash 2 per version instance.
+template <unsigned KN>
+static void run_vs(const JobConsts* jcs, int n_ver, uint32_t nonce, uint32_t* out)
+{
+    VsOps<KN> op{{make_pipe_mults()}};
+    uint32_t kw[kVsWords];
+    const uint32_t w3 = bswap32(nonce);
+    vs_schedule<KN>(jcs[0], w3, op, [&](int i, uint32_t v) { kw[i] = v; });
+    for (int v = 0; v < n_ver; v++) out[v] = vs_hash<KN>(jcs[v], jcs[0], w3, op, [&](int i) { return kw[i]; });
+}
+
 extern "C" {
+// e after round 60 of hash 2 for n_ver headers that differ only in their version field
+// (bytes 0..3 of hdr76 replaced by versions[v], little-endian), through the version-shared core.
+int fc_vs_e60_kn(const uint8_t hdr76[76], const uint32_t* versions, int n_ver, uint32_t nonce, unsigned knobs,
+                 uint32_t* e60_out)
+{
+    if (n_ver < 1 || n_ver > 64) return -1;
+    JobConsts jcs[64];
+    for (int v = 0; v < n_ver; v++) {
+        uint8_t h[76];
+        memcpy(h, hdr76, 76);
+        h[0] = versions[v]; h[1] = versions[v] >> 8; h[2] = versions[v] >> 16; h[3] = versions[v] >> 24;
+        consts_for(h, nullptr, &jcs[v]);
+    }
+#define VSSET(n, m) (KN_E | KN_W1 | KN_A | KN_W2 | KN_SP | KN_T1Z | OTD_KN_Z_EIGHTHS(n) | OTD_KN_VSZ_EIGHTHS(m))
+    switch (knobs) {
+        case 0: run_vs<0>(jcs, n_ver, nonce, e60_out); return 0;
+        case KN_E | KN_W1 | KN_A | KN_W2 | KN_T1X | KN_SP:
+            run_vs<KN_E | KN_W1 | KN_A | KN_W2 | KN_T1X | KN_SP>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(6, 0): run_vs<VSSET(6, 0)>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(6, 6): run_vs<VSSET(6, 6)>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(6, 4): run_vs<VSSET(6, 4)>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(6, 7): run_vs<VSSET(6, 7)>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(5, 6): run_vs<VSSET(5, 6)>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(7, 7): run_vs<VSSET(7, 7)>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(8, 0): run_vs<VSSET(8, 0)>(jcs, n_ver, nonce, e60_out); return 0;
+        case 1023: run_vs<1023>(jcs, n_ver, nonce, e60_out); return 0;
+        default: return -2;
+    }
+#undef VSSET
+}
 // e after round 60 of hash 2 via the unrolled folded path, V lanes (1, 2, 4),
 // under one of the knob sets below (the device variants use a subset of these).
 int fc_scan_e60_kn(const uint8_t hdr76[76], const uint32_t* nonces, int v, unsigned knobs, uint32_t* e60_out)

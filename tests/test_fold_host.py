@@ -18,7 +18,8 @@ IV7 = 0x5BE0CD19
 def fold():
     src = os.path.join(HERE, "_hostcheck", "fold_check.cpp")
     so = os.path.join(HERE, "_hostcheck", "libfoldcheck.so")
-    deps = [src] + [os.path.join(HERE, "..", "otedama_b200", "csrc", f) for f in ("scan_core.cuh", "sha256_core.cuh")]
+    deps = [src] + [os.path.join(HERE, "..", "otedama_b200", "csrc", f)
+                    for f in ("scan_core.cuh", "scan_vs_core.cuh", "sha256_core.cuh")]
     if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
         subprocess.check_call(["g++", "-O1", "-std=c++17", "-shared", "-fPIC", "-Wno-unknown-pragmas", "-o", so, src])
     L = ctypes.CDLL(so)
@@ -108,3 +109,42 @@ def test_midstate_digest_and_compare(fold, oracle):
             fold.fc_sha256d_mid(h76, n, t, out, ctypes.byref(le))
             assert out.raw == want
             assert bool(le.value) == oracle.less_or_equal(want, t) == (hv <= tv)
+
+
+def VSSET(n, m):
+    return ZSET(n) | (m << 20)
+
+
+VS_KNOB_SETS = [0, 1023, ADDS | KN["T1X"] | KN["SP"], VSSET(6, 0), VSSET(6, 6), VSSET(6, 4), VSSET(6, 7), VSSET(5, 6),
+                VSSET(7, 7), VSSET(8, 0)]
+
+
+def test_every_version_shared_variant_policy_is_host_checked():
+    """Each version-shared scan variant's knob set (csrc/scan_variants.h, OTD_VS_VARIANTS) is exercised below."""
+    import re
+    txt = open(os.path.join(HERE, "..", "otedama_b200", "csrc", "scan_variants.h")).read()
+    rows = re.findall(r"Y\((\d+), \"(\w+)\", (\d+), OTD_KN_VS\((\d+), (\d+)\), \d+, \d+\)", txt)
+    assert rows, "no version-shared variants found"
+    for idx, name, it, n, m in rows:
+        assert VSSET(int(n), int(m)) in VS_KNOB_SETS, name
+
+
+def test_version_shared_core_matches_oracle(fold, oracle):
+    """scan_vs_core.cuh: block 2's message schedule expanded once per nonce and reused by every BIP-320 version
+    instance gives, per instance, the same top digest word as hashing that instance's 80 bytes from scratch."""
+    rnd = random.Random(7)
+    mask = 0x1FFFE000
+    for case in range(120):
+        h76 = bytearray(rnd.randbytes(76))
+        n_ver = rnd.choice([1, 2, 3, 16, 33])
+        base = rnd.getrandbits(32) & ~mask
+        versions = [base | (rnd.getrandbits(32) & mask) for _ in range(n_ver)]
+        nonce = rnd.choice([0, 0xFFFFFFFF, rnd.getrandbits(32)])
+        arr = (ctypes.c_uint32 * n_ver)(*versions)
+        out = (ctypes.c_uint32 * n_ver)()
+        for knobs in (VS_KNOB_SETS if case % 6 == 0 else [VS_KNOB_SETS[case % len(VS_KNOB_SETS)]]):
+            assert fold.fc_vs_e60_kn(bytes(h76), arr, n_ver, nonce, knobs, out) == 0, knobs
+            for v, e in zip(versions, out):
+                hdr = struct.pack("<I", v) + bytes(h76[4:]) + struct.pack("<I", nonce)
+                h7 = struct.unpack(">I", oracle.sha256d(hdr)[28:32])[0]
+                assert (e + IV7) & 0xFFFFFFFF == h7, (knobs, hex(v))

@@ -270,9 +270,13 @@ def test_version_rolling_matches_oracle(miner, oracle):
         sh, _, _ = oracle.grind(oh, t, 0x10000000, 1 << 16, threads=NCPU)
         want += okey(sh)
     r = miner.scan(work)
-    assert r.hashes == 40 << 16 and r.launches == 40
+    assert r.hashes == 40 << 16 and r.launches == 3       # version-shared launches of 16 + 16 + 8 instances
     assert key(r.shares) == sorted(want) and len(want) > 100
     assert all(s.job_id == 9 for s in r.shares)
+    work.per_version_launch = True                        # the plain kernel, one launch per version instance
+    r1 = miner.scan(work)
+    assert r1.hashes == 40 << 16 and r1.launches == 40
+    assert key(r1.shares) == sorted(want)
 
 
 def test_version_rolling_default_count_covers_the_mask(miner, oracle):
@@ -281,13 +285,73 @@ def test_version_rolling_default_count_covers_the_mask(miner, oracle):
     t = oracle.target_from_difficulty(2.0 ** -20)
     r = miner.scan(miner.Work(header=mheader(miner, f), target=t, version_mask=0x0000E000, version_begin=1,
                               version_stride=3, nonce_count=1 << 14))
-    assert r.launches == 3
+    assert r.launches == 1 and r.hashes == 3 << 14       # one version-shared launch of the three instances
     want = []
     for k in (1, 4, 7):
         ver = oracle.bip320_version(f["version"], 0xE000, k)
         sh, _, _ = oracle.grind(oheader(oracle, f, version=ver), t, 0, 1 << 14)
         want += okey(sh)
     assert key(r.shares) == sorted(want)
+
+
+def test_version_shared_variants_match_oracle(miner, oracle):
+    """K1v (csrc/scan_vs_kernel.cuh): every version-shared variant, group sizes 1..16 incl. ragged tails
+    (17 = 16 + a lone instance on the plain kernel), a ragged nonce window, against the CPU oracle."""
+    c4 = W.config4_v2()
+    t = oracle.target_from_difficulty(2.0 ** -20)
+    names = miner.vs_variants()
+    assert names and miner.default_vs_variant() == 0
+    try:
+        for vi, name in enumerate(names):
+            miner.vs_select(vi)
+            for n_ver, begin, stride, nb, nc in ((2, 0, 1, 0, 5000), (16, 7, 3, 0xFFFF0000, 1 << 16),
+                                                 (17, 100, 1, 123, 3 * 1024 + 1), (33, 65000, 16, 1 << 31, 4096)):
+                if vi and n_ver not in (16, 17):
+                    continue
+                work = miner.Work(job_id=5, header=mheader(miner, c4), target=t, version_mask=c4["mask"],
+                                  version_begin=begin, version_count=n_ver, version_stride=stride, nonce_begin=nb,
+                                  nonce_count=nc)
+                want = []
+                for i in range(n_ver):
+                    ver = oracle.bip320_version(c4["version"], c4["mask"], begin + stride * i)
+                    sh, _, _ = oracle.grind(oheader(oracle, c4, version=ver), t, nb, nc, threads=NCPU)
+                    want += okey(sh)
+                r = miner.scan(work)
+                assert r.hashes == n_ver * nc, (name, n_ver)
+                assert r.launches == (n_ver + 15) // 16
+                assert key(r.shares) == sorted(want), (name, n_ver)
+    finally:
+        miner.vs_select(-1)
+    # switched off process-wide: the plain kernel per version gives the same set
+    miner.vs_select(-2)
+    try:
+        work = miner.Work(header=mheader(miner, c4), target=t, version_mask=c4["mask"], version_count=5, nonce_count=1 << 14)
+        r = miner.scan(work)
+        assert r.launches == 5
+    finally:
+        miner.vs_select(-1)
+    r2 = miner.scan(work)
+    assert r2.launches == 1 and key(r2.shares) == key(r.shares)
+
+
+def test_version_shared_groups_do_not_straddle_extranonce2(miner, oracle):
+    """extranonce2 x version: instances of different extranonce2 values have different merkle roots, so a
+    version-shared launch may only hold instances of ONE extranonce2 value."""
+    c3 = W.config3_v1()
+    t = oracle.target_from_difficulty(2.0 ** -20)
+    work, f = v1_work(miner, c3, target=t, extranonce2_begin=5, extranonce2_count=3, extranonce2_stride=2,
+                      version_mask=0x00006000, nonce_count=1 << 14)            # 4 versions per extranonce2
+    want = []
+    for e in (5, 7, 9):
+        root = oracle.v1_merkle_root(c3["coinb1"], c3["extranonce1"], oracle.extranonce2_bytes(e, c3["extranonce2_size"]),
+                                     c3["coinb2"], c3["branches"])
+        for k in range(4):
+            ver = oracle.bip320_version(c3["version"], 0x6000, k)
+            sh, _, _ = oracle.grind(oheader(oracle, f, version=ver, merkle_root=root), t, 0, 1 << 14, threads=NCPU)
+            want += okey(sh, extranonce2=e)
+    r = miner.scan(work)
+    assert r.launches == 3 and r.hashes == 12 << 14
+    assert key(r.shares) == sorted(want) and len(want) > 20
 
 
 # --------------------------------------- K3: extranonce2 roll + merkle root --
@@ -355,7 +419,9 @@ def test_extranonce2_times_version_space(miner, oracle):
     work, f = v1_work(miner, c3, target=t, extranonce2_begin=1, extranonce2_count=30, version_mask=W.BIP320_MASK,
                       version_begin=0, version_count=10, nonce_count=1 << 12)
     r = miner.scan(work)
-    assert r.launches == 300 and r.hashes == 300 << 12
+    # one version-shared launch per extranonce2 value (10 instances each), plus one where the 256-instance
+    # preparation batch boundary cuts a group in two (instances 250..255 | 256..259)
+    assert r.launches == 31 and r.hashes == 300 << 12
     want = []
     for e in range(1, 31):
         root = oracle.v1_merkle_root(c3["coinb1"], c3["extranonce1"], oracle.extranonce2_bytes(e, 8), c3["coinb2"],
@@ -530,7 +596,8 @@ def test_worker_runs_rolled_work_like_the_synchronous_scan(miner, oracle):
             got += part
         st = w.stats()
     assert key(got) == key(want.shares) and len(got) > 30
-    assert st.hashes_total == want.hashes == 45 << 14 and st.launches == 45
+    # 9 groups of 5 version instances; 2^16 candidates per launch -> 12 blocks of 1024 nonces x 5, then the rest
+    assert st.hashes_total == want.hashes == 45 << 14 and st.launches == 18
     assert all(s.job_id == 77 for s in got)
     # and a few of them against the oracle, end to end
     for s in got[:5]:
