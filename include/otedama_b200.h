@@ -33,7 +33,7 @@ extern "C" {
 #define OTD_ECUDA (-5)
 #define OTD_ERANGE (-34)
 
-#define OTD_ABI_VERSION 1
+#define OTD_ABI_VERSION 2 /* 2: job_id_str in otd_work_t / otd_share_t, job_id in otd_v1_submit_t */
 
 /* Last error message of the calling thread ("" if none). Never NULL. */
 const char* otd_last_error(void);
@@ -104,6 +104,7 @@ int otd_hash_headers(int device_index, const uint8_t* headers80, size_t n, uint8
  * miner.Work (internal/miner/worker.go:18-24) plus the search-space extension
  * north_star asks for.  A zero-initialised extension reproduces the reference:
  * one header, nonce-only search of all 2^32 nonces. */
+#define OTD_JOB_ID_MAX 64   /* bytes of an opaque pool job id incl. the terminating NUL */
 #define OTD_WORK_REPEAT 1u /* when the space is exhausted start over (the reference's
                               uint32 wrap, worker.go:279) instead of going idle */
 #define OTD_WORK_PER_VERSION_LAUNCH 2u /* rolled versions: one plain scan launch per version
@@ -142,6 +143,12 @@ typedef struct {
     uint32_t n_branches;
     uint32_t extranonce2_size;
     uint64_t extranonce2_begin, extranonce2_count, extranonce2_stride;
+    /* Stratum V1: the pool's job id exactly as mining.notify gave it (an opaque string, usually
+     * hex; NUL-terminated; "" when the job only has the numeric id above).  The library never
+     * parses it: it is echoed into every share of this work so that mining.submit can send it
+     * back verbatim.  (The reference squeezes the id through Sscanf("%d") into a uint32,
+     * internal/engine/run.go:1345-1348, which only works for decimal ids.) */
+    char job_id_str[OTD_JOB_ID_MAX];
 } otd_work_t;
 
 typedef struct {          /* miner.Share, worker.go:33-43 */
@@ -155,6 +162,7 @@ typedef struct {          /* miner.Share, worker.go:33-43 */
     uint64_t work_seq;    /* which set_work call this share belongs to (1-based) */
     int32_t device_index; /* -> Share.DeviceID via otd_device_info().id */
     int32_t reserved;
+    char job_id_str[OTD_JOB_ID_MAX]; /* the work's job_id_str, echoed */
 } otd_share_t;
 
 /* ------------------------------------------------------- job -> work glue --
@@ -189,8 +197,11 @@ int otd_work_from_v1_job(const char* job_id, uint32_t channel_id, const uint8_t 
  *     header order (header bytes = each word reversed);
  *   - version / nbits / ntime: big-endian hex of the u32 header fields;
  *   - coinbase = coinb1 || extranonce1 || extranonce2 || coinb2 (hex decoded).
- * job_id is parsed like the reference's applyJob (Sscanf "%d", run.go:1345-1348);
- * the share target comes from v1JobTarget(nbits, difficulty).  The decoded bytes
+ * job_id stays an opaque string (work->job_id_str, at most OTD_JOB_ID_MAX - 1 characters,
+ * echoed into the shares); work->job_id holds its value only when the whole string is a
+ * decimal number that fits 32 bits, else 0 — Stratum job ids are usually hex, which the
+ * reference's applyJob (Sscanf "%d", run.go:1345-1348; otd_work_from_v1_job mirrors it) would
+ * reject or truncate.  The share target comes from v1JobTarget(nbits, difficulty).  The decoded bytes
  * the work points to are placed in `scratch` (caller-owned; must outlive the use
  * of *work; otd_worker_set_work / otd_scan copy them).  Returns OTD_OK, or
  * OTD_ERANGE with *scratch_needed set when scratch_len is too small. */
@@ -212,7 +223,8 @@ int otd_work_from_v1_notify(const otd_v1_notify_t* notify, const char* extranonc
 
 /* A found share -> the hex fields of Stratum V1 mining.submit
  * (["worker", job_id, extranonce2, ntime, nonce] and, with version rolling, the
- * BIP-310 sixth field version_bits).  Replaces the body of session.Submit's
+ * BIP-310 sixth field version_bits).
+ *   job_id           = share.job_id_str verbatim, or "%u" of share.job_id when that is empty;  Replaces the body of session.Submit's
  * parameter formatting (internal/poolproto/stratumv1/stratumv1.go:336-346),
  * which today pads extranonce2 with zeros because the reference never rolls it:
  *   extranonce2_hex  = the extranonce2_size bytes that were placed in the coinbase
@@ -226,6 +238,7 @@ typedef struct {
     char ntime_hex[9];
     char nonce_hex[9];
     char version_bits_hex[9];
+    char job_id[OTD_JOB_ID_MAX];
 } otd_v1_submit_t;
 int otd_share_to_v1_submit(const otd_share_t* share, uint32_t extranonce2_size, uint32_t version_mask,
                            otd_v1_submit_t* out);
@@ -275,7 +288,12 @@ otd_worker_t* otd_worker_create(int device_index, const otd_worker_config_t* cfg
 int64_t otd_worker_set_work(otd_worker_t* w, const otd_work_t* work);
 /* The receive side of Start's `<-chan Share`: blocks up to timeout_ms
  * (0 = poll, < 0 = forever) until at least one share is available, the current
- * work is exhausted, or the worker is destroyed.  Returns the count written. */
+ * work has ENDED (its search space is exhausted, or its run failed) and no poll
+ * has returned for that yet, or the worker is destroyed.  Returns the count
+ * written.  The end of a work wakes exactly one empty poll: with 0 it if the
+ * space was exhausted, with OTD_ECUDA (message in otd_last_error) if the run
+ * failed; after that empty polls wait for their timeout again until
+ * otd_worker_set_work hands over new work (which also clears the failure). */
 int otd_worker_poll_shares(otd_worker_t* w, otd_share_t* out, int max_shares, int timeout_ms);
 /* Blocks until the current work is exhausted (or timeout). 1 = exhausted, 0 = timeout. */
 int otd_worker_wait_exhausted(otd_worker_t* w, int timeout_ms);
@@ -334,7 +352,14 @@ int otd_scan_headers(int device_index, const otd_header_t* headers, uint32_t n_h
  *     library lets only one run at a time — two scans using the array at once on
  *     the GPU would race, so do not try to overlap them from outside either
  *     (another process gets its own copy of the array).
- * Output is the same as otd_scan's for the same work (sorted by nonce); returns
+ *   - The clear, the kernel and the copies run on the legacy default stream
+ *     (stream 0): they order themselves after, and hold back, work the host
+ *     application has queued on its own blocking streams of that device; streams
+ *     created with cudaStreamNonBlocking are not affected.
+ * Output is the same as otd_scan's for the same work (sorted by nonce) as long as
+ * nothing was dropped.  When the device finds more than max_shares, the ones kept
+ * are whichever reached the ring first — an arbitrary subset that can differ from
+ * run to run (otd_scan keeps the lowest of the full set); *n_found tells.  Returns
  * the number of shares written. */
 #define OTD_NOALLOC_MAX_SHARES 4096u
 #define OTD_NOALLOC_SCRATCH_BYTES (256u + 40u * OTD_NOALLOC_MAX_SHARES) /* 164,096 bytes per GPU */

@@ -20,6 +20,7 @@ OTD_OK, OTD_EINVAL, OTD_ENODEV, OTD_ENOMEM, OTD_EBUSY, OTD_ECUDA, OTD_ERANGE = 0
 OTD_WORK_REPEAT = 1
 OTD_WORK_PER_VERSION_LAUNCH = 2
 OTD_NOALLOC_MAX_SHARES = 4096
+OTD_JOB_ID_MAX = 64
 
 
 class OtdError(RuntimeError):
@@ -54,7 +55,8 @@ class CWork(Structure):
                 ("coinb2", c_void_p), ("coinb2_len", c_uint32),
                 ("merkle_branches", c_void_p), ("n_branches", c_uint32),
                 ("extranonce2_size", c_uint32), ("extranonce2_begin", c_uint64),
-                ("extranonce2_count", c_uint64), ("extranonce2_stride", c_uint64)]
+                ("extranonce2_count", c_uint64), ("extranonce2_stride", c_uint64),
+                ("job_id_str", c_char * OTD_JOB_ID_MAX)]
 
 
 class CV1Notify(Structure):
@@ -66,12 +68,13 @@ class CV1Notify(Structure):
 class CShare(Structure):
     _fields_ = [("channel_id", c_uint32), ("job_id", c_uint32), ("nonce", c_uint32), ("ntime", c_uint32),
                 ("version", c_uint32), ("hash", c_uint8 * 32), ("extranonce2", c_uint64),
-                ("work_seq", c_uint64), ("device_index", c_int32), ("reserved", c_int32)]
+                ("work_seq", c_uint64), ("device_index", c_int32), ("reserved", c_int32),
+                ("job_id_str", c_char * OTD_JOB_ID_MAX)]
 
 
 class CV1Submit(Structure):
     _fields_ = [("extranonce2_hex", c_char * 33), ("ntime_hex", c_char * 9), ("nonce_hex", c_char * 9),
-                ("version_bits_hex", c_char * 9)]
+                ("version_bits_hex", c_char * 9), ("job_id", c_char * OTD_JOB_ID_MAX)]
 
 
 class CWorkerConfig(Structure):

@@ -78,6 +78,23 @@ extern "C" int otd_device_count(void)
     return n;
 }
 
+// Synchronous entry points make their device current for the duration of the call and put the
+// caller's device back on return (a host application has its own idea of the current device).
+struct DeviceScope {
+    int prev = -1;
+    DeviceScope()
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess) {
+            prev = -1;
+            cudaGetLastError();
+        }
+    }
+    ~DeviceScope()
+    {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
 static int check_device(int idx)
 {
     int n = otd_device_count();
@@ -485,10 +502,30 @@ extern "C" int otd_work_from_v1_notify(const otd_v1_notify_t* n, const char* ext
     uint8_t prev_wire[32];
     if (strlen(n->prevhash_hex) != 64 || hex_decode(n->prevhash_hex, prev_wire, 32) != 32)
         return fail(OTD_EINVAL, "otd_work_from_v1_notify: prevhash must be 64 hex characters");
+    if (strlen(n->job_id) >= OTD_JOB_ID_MAX)
+        return fail(OTD_EINVAL, "otd_work_from_v1_notify: job id longer than " + std::to_string(OTD_JOB_ID_MAX - 1) + " characters");
     otd_work_t w;
-    uint8_t zero[32] = {0};
-    int rc = otd_work_from_v1_job(n->job_id, channel_id, zero, ntime, nbits, difficulty, &w);  // id, target, time, bits
-    if (rc) return rc;
+    memset(&w, 0, sizeof w);
+    int rc = otd_v1_job_target(nbits, difficulty, w.target);
+    if (rc) return fail(rc, std::string("engine: bad target for job \"") + n->job_id + "\": " + otd_last_error());
+    // The pool's job id is an opaque string: kept verbatim for mining.submit.  The numeric id is a convenience
+    // for decimal ids only (what the reference's uint32 JobID can hold); anything else leaves it 0.
+    snprintf(w.job_id_str, sizeof w.job_id_str, "%s", n->job_id);
+    {
+        unsigned long long v = 0;
+        const char* q = n->job_id;
+        bool dec = *q != 0;
+        for (; *q && dec; q++) {
+            dec = *q >= '0' && *q <= '9';
+            if (dec) v = v * 10 + (unsigned)(*q - '0');
+            if (v > 0xffffffffull) dec = false;
+        }
+        w.job_id = dec ? (uint32_t)v : 0u;
+    }
+    w.channel_id = channel_id;
+    w.header.time = ntime;
+    w.header.bits = nbits;
+    w.nbits = nbits;
     w.header.version = version;
     for (int wi = 0; wi < 8; wi++)      // each 4-byte word reversed -> header (internal) byte order
         for (int b = 0; b < 4; b++) w.header.prev_hash[4 * wi + b] = prev_wire[4 * wi + 3 - b];
@@ -599,6 +636,7 @@ static int copy_work(const otd_work_t* in, WorkCopy* wc)
 {
     if (!in) return fail(OTD_EINVAL, "work is NULL");
     wc->w = *in;
+    wc->w.job_id_str[OTD_JOB_ID_MAX - 1] = 0;
     const otd_work_t& w = wc->w;
     wc->nonce_count = w.nonce_count ? w.nonce_count : (1ull << 32);
     if ((uint64_t)w.nonce_begin + wc->nonce_count > (1ull << 32))
@@ -613,6 +651,8 @@ static int copy_work(const otd_work_t* in, WorkCopy* wc)
         const uint64_t avail = (total - w.version_begin + wc->ver_stride - 1) / wc->ver_stride;
         wc->n_ver = w.version_count ? w.version_count : avail;
         if (wc->n_ver > avail) return fail(OTD_EINVAL, "version_count exceeds the mask's index space");
+        // the preparation kernel indexes version instances with 32-bit arithmetic; BIP-320 uses 16 bits
+        if (wc->n_ver > (1ull << 31)) return fail(OTD_EINVAL, "version slice larger than 2^31 indices (narrow the mask or set version_count)");
     } else if (w.version_count > 1) {
         return fail(OTD_EINVAL, "version_count > 1 without a version_mask");
     }
@@ -690,6 +730,10 @@ extern "C" int otd_share_to_v1_submit(const otd_share_t* share, uint32_t extrano
     snprintf(out->ntime_hex, sizeof out->ntime_hex, "%08x", share->ntime);
     snprintf(out->nonce_hex, sizeof out->nonce_hex, "%08x", share->nonce);
     if (version_mask) snprintf(out->version_bits_hex, sizeof out->version_bits_hex, "%08x", share->version & version_mask);
+    if (share->job_id_str[0] && memchr(share->job_id_str, 0, sizeof share->job_id_str))
+        snprintf(out->job_id, sizeof out->job_id, "%s", share->job_id_str);
+    else
+        snprintf(out->job_id, sizeof out->job_id, "%u", share->job_id);
     return OTD_OK;
 }
 
@@ -912,6 +956,7 @@ class Engine {
             memset(&sh, 0, sizeof sh);
             sh.channel_id = wc.w.channel_id;
             sh.job_id = wc.w.job_id;
+            memcpy(sh.job_id_str, wc.w.job_id_str, sizeof sh.job_id_str);
             sh.nonce = s.h_ent[i].nonce;
             sh.ntime = wc.w.header.time;
             const uint32_t vi = s.h_ent[i].instance - s.inst0;  // which of the launch's version instances
@@ -1058,6 +1103,7 @@ extern "C" int otd_scan(int device_index, const otd_work_t* work, int kernel_var
                         uint32_t max_shares, uint64_t* n_found, uint64_t* hashes, double* device_ms,
                         uint64_t* launches)
 {
+    DeviceScope scope;  // the caller's current device is restored on return
     WorkCopy wc;
     int rc = copy_work(work, &wc);
     if (rc) return rc;
@@ -1093,6 +1139,7 @@ extern "C" int otd_scan_headers(int device_index, const otd_header_t* headers, u
                                 int kernel_variant, otd_share_t* out, uint32_t max_shares, uint64_t* n_found,
                                 uint64_t* hashes, double* device_ms, uint64_t* launches)
 {
+    DeviceScope scope;  // the caller's current device is restored on return
     if (!headers || !target || n_headers == 0) return fail(OTD_EINVAL, "otd_scan_headers: bad argument");
     if (max_shares && !out) return fail(OTD_EINVAL, "otd_scan_headers: out is NULL");
     if (nonce_count == 0) nonce_count = 1ull << 32;
@@ -1167,6 +1214,7 @@ extern "C" int otd_prepare_instances(int device_index, const otd_work_t* work, u
                                      uint8_t* merkle_roots, uint32_t* versions, uint64_t* extranonce2s,
                                      uint8_t* midstates)
 {
+    DeviceScope scope;  // the caller's current device is restored on return
     WorkCopy wc;
     int rc = copy_work(work, &wc);
     if (rc) return rc;
@@ -1199,6 +1247,7 @@ extern "C" int otd_prepare_instances(int device_index, const otd_work_t* work, u
 // ------------------------------------------------------------ hash_headers --
 extern "C" int otd_hash_headers(int device_index, const uint8_t* headers80, size_t n, uint8_t* hashes32)
 {
+    DeviceScope scope;  // the caller's current device is restored on return
     int rc = check_device(device_index);
     if (rc) return rc;
     if (n == 0) return OTD_OK;
@@ -1232,6 +1281,7 @@ struct otd_worker : ShareSink {
     std::atomic<uint64_t> seq{0};
     std::atomic<bool> stop{false};
     bool exhausted = false;
+    uint64_t exhausted_reported = 0;  // work_seq whose end (exhausted or failed) a poll has already returned for
     std::deque<otd_share_t> queue;
     std::atomic<uint64_t> hashes{0}, shares{0}, dropped{0}, launches{0}, candidates{0};
     double device_ms = 0;
@@ -1293,6 +1343,7 @@ struct otd_worker : ShareSink {
 
 extern "C" otd_worker_t* otd_worker_create(int device_index, const otd_worker_config_t* cfg)
 {
+    DeviceScope scope;  // the caller's current device is restored on return
     std::unique_ptr<otd_worker> w(new otd_worker());
     w->dev = device_index;
     otd_worker_config_t c;
@@ -1329,6 +1380,7 @@ extern "C" int64_t otd_worker_set_work(otd_worker_t* w, const otd_work_t* work)
     std::lock_guard<std::mutex> g(w->mu);
     w->work = wc;
     w->exhausted = false;
+    w->thread_error.clear();  // a failure belongs to the work it happened on
     const uint64_t s = w->seq.fetch_add(1) + 1;
     w->cv_work.notify_all();
     w->cv_share.notify_all();
@@ -1339,7 +1391,11 @@ extern "C" int otd_worker_poll_shares(otd_worker_t* w, otd_share_t* out, int max
 {
     if (!w || !out || max_shares <= 0) return fail(OTD_EINVAL, "otd_worker_poll_shares: bad argument");
     std::unique_lock<std::mutex> lk(w->mu);
-    auto ready = [&] { return !w->queue.empty() || w->exhausted || w->stop.load(); };
+    // Wake for: a share, shutdown, or the END of the current work (exhausted / failed) that no poll has
+    // returned for yet.  Once that end has been reported, an empty poll honours its timeout again instead
+    // of returning at once for as long as the worker stays idle.
+    auto ended_unreported = [&] { return w->exhausted && w->exhausted_reported != w->seq.load(); };
+    auto ready = [&] { return !w->queue.empty() || ended_unreported() || w->stop.load(); };
     if (timeout_ms < 0) w->cv_share.wait(lk, ready);
     else if (timeout_ms > 0) w->cv_share.wait_for(lk, std::chrono::milliseconds(timeout_ms), ready);
     int n = 0;
@@ -1347,7 +1403,10 @@ extern "C" int otd_worker_poll_shares(otd_worker_t* w, otd_share_t* out, int max
         out[n++] = w->queue.front();
         w->queue.pop_front();
     }
-    if (n == 0 && !w->thread_error.empty()) return fail(OTD_ECUDA, w->thread_error);
+    if (n == 0 && ended_unreported()) {
+        w->exhausted_reported = w->seq.load();
+        if (!w->thread_error.empty()) return fail(OTD_ECUDA, w->thread_error);  // reported once per failed work
+    }
     return n;
 }
 
@@ -1392,6 +1451,7 @@ extern "C" int otd_worker_device_index(otd_worker_t* w) { return w ? w->dev : fa
 
 extern "C" int otd_worker_destroy(otd_worker_t* w)
 {
+    DeviceScope scope;  // the caller's current device is restored on return
     if (!w) return OTD_OK;
     {
         std::lock_guard<std::mutex> g(w->mu);
@@ -1427,6 +1487,7 @@ static cudaError_t launch_peak(int grid, int iters, uint32_t* sink, long long* c
 
 extern "C" int otd_int_peak(int device_index, int mode, int iters, double* ops_per_s, double* sm_mhz, double* ms_out)
 {
+    DeviceScope scope;  // the caller's current device is restored on return
     int rc = check_device(device_index);
     if (rc) return rc;
     if (mode < 0 || mode >= IPM_COUNT) return fail(OTD_EINVAL, "otd_int_peak: unknown mode");
@@ -1516,6 +1577,7 @@ static int noalloc_setup(int dev, unsigned char** out)
 extern "C" int otd_scan_noalloc(int device_index, const otd_work_t* work, int kernel_variant, otd_share_t* out,
                                 uint32_t max_shares, uint64_t* n_found, uint64_t* hashes)
 {
+    DeviceScope scope;  // the caller's current device is restored on return
     if (!work) return fail(OTD_EINVAL, "otd_scan_noalloc: work is NULL");
     if (max_shares && !out) return fail(OTD_EINVAL, "otd_scan_noalloc: out is NULL");
     if (max_shares > OTD_NOALLOC_MAX_SHARES)
@@ -1568,6 +1630,7 @@ extern "C" int otd_scan_noalloc(int device_index, const otd_work_t* work, int ke
             memset(&sh, 0, sizeof sh);
             sh.channel_id = work->channel_id;
             sh.job_id = work->job_id;
+            memcpy(sh.job_id_str, work->job_id_str, sizeof sh.job_id_str - 1);
             sh.nonce = chunk[i].nonce;
             sh.ntime = work->header.time;
             sh.version = work->header.version;

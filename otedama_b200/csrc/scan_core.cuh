@@ -121,6 +121,11 @@ enum : unsigned {
                      // Applied to KN_Z_EIGHTHS(n)/8 of the rounds (the rest use the KN_T1X form): the best
                      // FMA:ALU balance is an interior point (measured: 5/8..6/8).
     KN_Z_SHIFT = 16u,  // bits 16..19: n of KN_Z_EIGHTHS(n), 1..8
+    KN_KCONST = 1u << 26,  // rounds 16/17 of hash 1 (K + W is a job constant in the constant bank): fixed one-IADD3 form.
+                           // Without it the KN_T1Z placement of these two rounds is picked from the VALUE of the
+                           // constant, i.e. by a run-time (uniform) branch over two copies of the round
+    KN_T7Z = 1u << 27,     // kernel level: when the target's top word is zero (share difficulty >= 1) the early-reject
+                           // test is "e60 == -IV7" (one ISETP) instead of add + byte swap + compare
     KN_COMPACT = 2048u,  // partially rolled body (scan_core_compact): the three fully generic 16-round blocks
                          // share one loop body so the code stays well inside the instruction cache
 };
@@ -271,6 +276,16 @@ struct Ops {
         const uint32_t hk = h + k;
         return add3_if(KN & KN_T1, hk, S1(e), ch(e, f, g));
     }
+    // same for a job constant whose value is not known at compile time
+    OTD_HD uint32_t t1_kc(uint32_t h, uint32_t e, uint32_t f, uint32_t g, uint32_t k) const
+    {
+        if (!(KN & KN_KCONST)) return t1_k(h, e, f, g, k);
+        if (KN & (KN_T1X | KN_T1Z)) {
+            const uint32_t y = h + S1(e) + k;
+            return fma_add(y, ch(e, f, g), m.one);
+        }
+        return add3_if(KN & KN_T1, h + k, S1(e), ch(e, f, g));
+    }
     OTD_HD void finish(uint32_t t1, uint32_t a, uint32_t b, uint32_t c, uint32_t& d, uint32_t& h) const
     {
         d = add_if(KN & KN_E, d, t1);
@@ -300,6 +315,17 @@ OTD_HD void rnd(const Ops<KN>& op, const vw<V>& a, const vw<V>& b, const vw<V>& 
 #pragma unroll
     for (int i = 0; i < V; i++) {
         const uint32_t t1 = op.t1_k(h.x[i], e.x[i], f.x[i], g.x[i], kw);
+        op.finish(t1, a.x[i], b.x[i], c.x[i], d.x[i], h.x[i]);
+    }
+}
+// ... with K + W a job constant (constant bank, value unknown at compile time)
+template <int V, unsigned KN>
+OTD_HD void rnd_kc(const Ops<KN>& op, const vw<V>& a, const vw<V>& b, const vw<V>& c, vw<V>& d, const vw<V>& e,
+                   const vw<V>& f, const vw<V>& g, vw<V>& h, uint32_t kw)
+{
+#pragma unroll
+    for (int i = 0; i < V; i++) {
+        const uint32_t t1 = op.t1_kc(h.x[i], e.x[i], f.x[i], g.x[i], kw);
         op.finish(t1, a.x[i], b.x[i], c.x[i], d.x[i], h.x[i]);
     }
 }
@@ -504,8 +530,8 @@ OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
 #pragma unroll
     for (int i = 34; i < 64; i++) w[i] = sched(op, w[i - 2], w[i - 7], w[i - 15], w[i - 16]);
 
-    rnd(op, h, a, b, c, d, e, f, g, jc.kw16);
-    rnd(op, g, h, a, b, c, d, e, f, jc.kw17);
+    rnd_kc(op, h, a, b, c, d, e, f, g, jc.kw16);
+    rnd_kc(op, g, h, a, b, c, d, e, f, jc.kw17);
     rnd(op, f, g, h, a, b, c, d, e, w[18], Kc(18));
     rnd(op, e, f, g, h, a, b, c, d, w[19], Kc(19));
     rnd(op, d, e, f, g, h, a, b, c, w[20], Kc(20));

@@ -96,7 +96,9 @@ scan_kernel(const __grid_constant__ JobConsts jc, const __grid_constant__ PipeMu
 #pragma unroll
         for (int v = 0; v < V; v++) {
             // most significant word of the little-endian hash integer vs the target's
-            const bool cnd = __byte_perm(e60.x[v] + IV7, 0, 0x0123) <= jc.target[7];
+            bool cnd;
+            if ((KN & KN_T7Z) && jc.target[7] == 0u) cnd = e60.x[v] == kE60ForZeroTop;   // warp-uniform choice
+            else cnd = __byte_perm(e60.x[v] + IV7, 0, 0x0123) <= jc.target[7];
             cmask |= (cnd ? 1u : 0u) << v;
         }
         if (__any_sync(0xffffffffu, cmask != 0)) {  // rare, warp-uniform

@@ -35,7 +35,10 @@ struct VsParams;
     X(4, "c_alu_b4", 1, 16, otd::KN_COMPACT, false, 4, 256)                                         \
     X(5, "add_z6_v2_b2", 2, 8, OTD_KN_BEST, false, 2, 256)                                          \
     X(6, "h_alu", 1, 16, 0u, true, 5, 256)                                                          \
-    X(7, "h_add_sp", 1, 16, OTD_KN_SPX, true, 5, 256)
+    X(7, "h_add_sp", 1, 16, OTD_KN_SPX, true, 5, 256)                                               \
+    X(8, "x_z6_kc_b4", 1, 16, OTD_KN_BEST | otd::KN_KCONST, false, 4, 256)                          \
+    X(9, "x_z6_t7z_b4", 1, 16, OTD_KN_BEST | otd::KN_T7Z, false, 4, 256)                            \
+    X(10, "x_z6_kc_t7z_b4", 1, 16, OTD_KN_BEST | otd::KN_KCONST | otd::KN_T7Z, false, 4, 256)
 
 #define OTD_NUM_PRODUCTION_VARIANTS 6
 #define OTD_DEFAULT_VARIANT 0
@@ -44,13 +47,18 @@ struct VsParams;
 // the full SHA-256d.  OTD_KN_VS(n, m): the shipped add placement with n/8 of the immediate-constant rounds and
 // m/8 of the shared-schedule rounds built from IMADs only (m = 0 reads as 8/8).
 #define OTD_KN_VS(n, m) (OTD_KN_ADDS | otd::KN_SP | otd::KN_T1Z | OTD_KN_Z_EIGHTHS(n) | OTD_KN_VSZ_EIGHTHS(m))
+// Measured on B200 (profiles/r2_vs_sweep_*.log), GH/s per GPU on 16 versions x 2^28 nonces (plain kernel per version: 9.53):
+//   vs_z7_r7_b4 11.10 | vs_z6_r8_b4 11.07 | vs_z6_r6_b4 11.00 | vs_z6_r4_b4 10.92 | 5 blocks/SM (f20) 11.09 |
+//   192-thread blocks x 6 10.55 | 128 x 9 10.38 — more warps than 32 per SM buy nothing, smaller blocks lose.
+// With 32 instances per launch (shipped; 32 x 2^27): vs_z7_r7_b4 11.21 | z6_r8 11.19 | f20_b5 11.19 | z6_r6 11.11;
+// hash-1 rounds 24..63 rolled into an 8-round loop body (l1, 39 KB of code instead of 47): 10.96-11.05 — the
+// instruction cache is not what holds the kernel back (ncu: hit rate 93 %, no_instruction 0.3 of 10.6 cycles per issue).
 #define OTD_VS_VARIANTS(Y)                                  \
-    Y(0, "vs_z6_r6_b4", 4, OTD_KN_VS(6, 6), 4, 256)         \
-    Y(1, "vs_z6_r8_b4", 4, OTD_KN_VS(6, 0), 4, 256)         \
-    Y(2, "vs_z6_r4_b4", 4, OTD_KN_VS(6, 4), 4, 256)         \
-    Y(3, "vs_z6_r7_b4", 4, OTD_KN_VS(6, 7), 4, 256)         \
-    Y(4, "vs_z5_r6_b4", 4, OTD_KN_VS(5, 6), 4, 256)         \
-    Y(5, "vs_z7_r7_b4", 4, OTD_KN_VS(7, 7), 4, 256)
+    Y(0, "vs_z7_r7_b4", 4, OTD_KN_VS(7, 7), 4, 256)         \
+    Y(1, "vs_z6_r6_b4", 4, OTD_KN_VS(6, 6), 4, 256)         \
+    Y(2, "vs_z6_r8_b4", 4, OTD_KN_VS(6, 0), 4, 256)         \
+    Y(3, "vs_z7_r7_f20_b5", 4, OTD_KN_VS(7, 7) | otd::KN_VS_F20, 5, 256) \
+    Y(4, "vs_z7_r8_l1_b4", 4, OTD_KN_VS(7, 0) | otd::KN_VS_LOOP1, 4, 256)
 #define OTD_DEFAULT_VS_VARIANT 0
 
 typedef cudaError_t (*otd_scan_launch_fn)(const otd::JobConsts&, uint32_t nonce_begin,

@@ -20,8 +20,11 @@
 
 namespace otd {
 
-constexpr int kVsFirstRound = 18;                 // first round whose K+W comes from the shared schedule
-constexpr int kVsWords = 64 - kVsFirstRound;      // 46 words per nonce
+// First round whose K+W is parked in shared memory: 18 (46 words per nonce), or 20 with KN_VS_F20 — rounds 18
+// and 19 then travel in two registers across the version loop, and 44 words per nonce let five 256-thread blocks
+// (40 warps) share an SM's 228 KB instead of four.
+template <unsigned KN> OTD_HD constexpr int vs_first_round() { return (KN & (1u << 24)) ? 20 : 18; }
+template <unsigned KN> OTD_HD constexpr int vs_words() { return 64 - vs_first_round<KN>(); }
 
 // Knob bits private to the version-shared core (above scan_core.cuh's).
 #define OTD_KN_VSZ_EIGHTHS(n) ((unsigned)(n) << 20)
@@ -30,6 +33,10 @@ enum : unsigned {
                          // rounds whose t1 is built from IMADs only (h + kw, Sigma1 + Ch, sum); the rest keep one
                          // IADD3 (h + Sigma1 + kw) on the ALU pipe — the FMA:ALU balance knob of scan_core.cuh's
                          // KN_T1Z, for rounds that need no immediate
+    KN_VS_F20 = 1u << 24,  // see vs_first_round()
+    KN_VS_LOOP1 = 1u << 25,  // hash 1 rounds 24..63 as five trips of one 8-round body instead of 40 unrolled rounds:
+                             // these rounds carry no schedule window (K+W comes from shared memory), so rolling
+                             // them costs no registers and takes ~10 KB off the instruction-cache footprint
 };
 
 template <unsigned KN>
@@ -81,6 +88,7 @@ struct VsOps : Ops<KN> {
 // K[i] + W[i] of hash 1's block 2 for i = 18..63, handed to put(i - 18, value).
 // Only the version-independent members of jc are read (w16, w17, c18, c19, c31,
 // c32): any instance of the job will do.
+// put(i, value) receives i = round - 18 (so i = 0, 1 are the two register-carried words under KN_VS_F20).
 template <unsigned KN, class Put>
 OTD_HD void vs_schedule(const JobConsts& jc, uint32_t w3s, const Ops<KN>& op, Put&& put)
 {
@@ -108,7 +116,7 @@ OTD_HD void vs_schedule(const JobConsts& jc, uint32_t w3s, const Ops<KN>& op, Pu
 #pragma unroll
     for (int i = 34; i < 64; i++) w[i] = sched(op, w[i - 2], w[i - 7], w[i - 15], w[i - 16]);
 #pragma unroll
-    for (int i = kVsFirstRound; i < 64; i++) put(i - kVsFirstRound, w[i].x[0] + Kc(i));
+    for (int i = 18; i < 64; i++) put(i - 18, w[i].x[0] + Kc(i));
 }
 
 // ---- phase B: once per (nonce, version instance) -------------------------------
@@ -150,7 +158,7 @@ OTD_HD uint32_t vs_hash(const JobConsts& jv, const JobConsts& js, uint32_t w3s, 
     rnd(op, a, b, c, d, e, f, g, h, Kc(15) + 0x280u);
     op.rnd_c(h, a, b, c, d, e, f, g, js.kw16);
     op.rnd_c(g, h, a, b, c, d, e, f, js.kw17);
-#define OTD_VS_R(i, a, b, c, d, e, f, g, h) op.rnd_r(a, b, c, d, e, f, g, h, get((i) - kVsFirstRound), Kc(i))
+#define OTD_VS_R(i, a, b, c, d, e, f, g, h) op.rnd_r(a, b, c, d, e, f, g, h, get((i) - 18), Kc(i))
     OTD_VS_R(18, f, g, h, a, b, c, d, e);
     OTD_VS_R(19, e, f, g, h, a, b, c, d);
     OTD_VS_R(20, d, e, f, g, h, a, b, c);
@@ -166,11 +174,28 @@ OTD_HD uint32_t vs_hash(const JobConsts& jv, const JobConsts& js, uint32_t w3s, 
     OTD_VS_R((R) + 5, c, d, e, f, g, h, a, b); \
     OTD_VS_R((R) + 6, b, c, d, e, f, g, h, a); \
     OTD_VS_R((R) + 7, a, b, c, d, e, f, g, h);
-    OTD_VS_R8(24)
-    OTD_VS_R8(32)
-    OTD_VS_R8(40)
-    OTD_VS_R8(48)
-    OTD_VS_R8(56)
+    if (KN & KN_VS_LOOP1) {
+        // the placement pattern of rounds 24..31 repeats in every trip (ksel must be a compile-time constant)
+#define OTD_VS_RL(j, a, b, c, d, e, f, g, h) op.rnd_r(a, b, c, d, e, f, g, h, get(base - 18 + (j)), Kc(24 + (j)))
+#pragma unroll 1
+        for (int base = 24; base < 64; base += 8) {
+            OTD_VS_RL(0, h, a, b, c, d, e, f, g);
+            OTD_VS_RL(1, g, h, a, b, c, d, e, f);
+            OTD_VS_RL(2, f, g, h, a, b, c, d, e);
+            OTD_VS_RL(3, e, f, g, h, a, b, c, d);
+            OTD_VS_RL(4, d, e, f, g, h, a, b, c);
+            OTD_VS_RL(5, c, d, e, f, g, h, a, b);
+            OTD_VS_RL(6, b, c, d, e, f, g, h, a);
+            OTD_VS_RL(7, a, b, c, d, e, f, g, h);
+        }
+#undef OTD_VS_RL
+    } else {
+        OTD_VS_R8(24)
+        OTD_VS_R8(32)
+        OTD_VS_R8(40)
+        OTD_VS_R8(48)
+        OTD_VS_R8(56)
+    }
 #undef OTD_VS_R8
 #undef OTD_VS_R
     // the role order now is (h,a,b,c,d,e,f,g) = (A,B,C,D,E,F,G,H); hash 2 on the digest (state + midstate)

@@ -10,7 +10,7 @@
 // only: internal/miner/worker.go:216-282).
 //
 // Bound: integer ALU issue, like K1.  Shared memory is private scratch (each
-// thread reads back only what it wrote: no barrier), 46 x BLOCK words per block;
+// thread reads back only what it wrote: no barrier), 46 (or 44) x BLOCK words per block;
 // the instances' constants arrive as a __grid_constant__ array and are read
 // through the constant bank with the (warp-uniform) instance index.
 #pragma once
@@ -19,7 +19,7 @@
 
 namespace otd {
 
-constexpr int kVsMaxVersions = 16;  // instances per launch: 16 x 172 B of kernel parameters
+constexpr int kVsMaxVersions = 32;  // instances per launch: 32 x 172 B of kernel parameters
 
 struct VsParams {
     JobConsts jc[kVsMaxVersions];
@@ -35,7 +35,8 @@ scan_vs_kernel(const __grid_constant__ VsParams p, const __grid_constant__ PipeM
 {
     if (*reinterpret_cast<const volatile unsigned int*>(stop_gen) != my_gen) return;
 
-    __shared__ uint32_t kw_smem[kVsWords * BLOCK];  // word i of this thread: kw_smem[i * BLOCK + threadIdx.x]
+    constexpr int kSkip = vs_first_round<KN>() - 18;  // leading words carried in registers instead
+    __shared__ uint32_t kw_smem[vs_words<KN>() * BLOCK];  // word i of this thread: kw_smem[i * BLOCK + threadIdx.x]
     uint32_t* const col = kw_smem + threadIdx.x;
 
     VsOps<KN> op{{pm}};
@@ -48,7 +49,11 @@ scan_vs_kernel(const __grid_constant__ VsParams p, const __grid_constant__ PipeM
         const unsigned long long idx = tile0 + (unsigned long long)it * BLOCK;
         const uint32_t nonce = nonce_begin + (uint32_t)idx;
         const uint32_t w3 = __byte_perm(nonce, 0, 0x0123);
-        vs_schedule<KN>(p.jc[0], w3, op, [&](int i, uint32_t v) { col[i * BLOCK] = v; });
+        uint32_t head[kSkip ? kSkip : 1];
+        vs_schedule<KN>(p.jc[0], w3, op, [&](int i, uint32_t v) {
+            if (i < kSkip) head[i] = v;
+            else col[(i - kSkip) * BLOCK] = v;
+        });
 
 #pragma unroll 1
         for (uint32_t v = 0; v < n_ver; v++) {
@@ -57,7 +62,9 @@ scan_vs_kernel(const __grid_constant__ VsParams p, const __grid_constant__ PipeM
             // address the compiler cannot prove loop-invariant (pm.zero is a run-time 0) stops it hoisting the
             // loads out of the version loop and forwarding the stored values to them.
             const uint32_t* const colv = col + (v & pm.zero);
-            const uint32_t e60 = vs_hash<KN>(jv, p.jc[0], w3, op, [&](int i) { return colv[i * BLOCK]; });
+            const uint32_t e60 = vs_hash<KN>(jv, p.jc[0], w3, op, [&](int i) {
+                return i < kSkip ? head[i] : colv[(i - kSkip) * BLOCK];
+            });
             const bool cnd = __byte_perm(e60 + IV7, 0, 0x0123) <= p.jc[0].target[7];
             if (__any_sync(0xffffffffu, cnd)) {  // rare, warp-uniform
                 uint32_t dig[8];

@@ -42,6 +42,7 @@ class Job:
 def _work_from_c(cw: CWork) -> miner.Work:
     h = cw.header
     return miner.Work(job_id=cw.job_id, channel_id=cw.channel_id, nbits=cw.nbits, target=bytes(cw.target),
+                      job_id_str=cw.job_id_str.decode("utf-8", "replace"),
                       header=miner.Header(h.version, bytes(h.prev_hash), bytes(h.merkle_root), h.time, h.bits, 0))
 
 
@@ -123,12 +124,13 @@ def v1_submit_params(share: miner.Share, work: miner.Work, worker_name: str = "o
     """The mining.submit parameter list for a share of a V1 work unit (stratumv1.go:336-346 with the
     rolled extranonce2 instead of zero padding; a sixth BIP-310 version_bits field when rolling)."""
     cs = capi.CShare(share.channel_id, share.job_id, share.nonce, share.ntime, share.version,
-                     (ctypes.c_uint8 * 32)(*share.hash), share.extranonce2, share.work_seq, 0, 0)
+                     (ctypes.c_uint8 * 32)(*share.hash), share.extranonce2, share.work_seq, 0, 0,
+                     share.job_id_str.encode())
     out = capi.CV1Submit()
     size = work.extranonce2_size if work.coinb1 is not None else 0
     if lib().otd_share_to_v1_submit(ctypes.byref(cs), size, work.version_mask, ctypes.byref(out)) < 0:
         raise EngineError(capi.last_error())
-    params = [worker_name, str(share.job_id), out.extranonce2_hex.decode(), out.ntime_hex.decode(),
+    params = [worker_name, out.job_id.decode(), out.extranonce2_hex.decode(), out.ntime_hex.decode(),
               out.nonce_hex.decode()]
     if work.version_mask:
         params.append(out.version_bits_hex.decode())
@@ -155,17 +157,41 @@ def partition_work(work: miner.Work, g: int, G: int) -> miner.Work:
 # ----------------------------------------------------------------------------
 # startMinerWorkers / mergeShares  (internal/engine/setup.go:56-78, fanin.go:20-68)
 # ----------------------------------------------------------------------------
-def start_miner_workers(devices, log=lambda level, msg: None, cfg: "miner.WorkerConfig | None" = None):
-    """One started worker per SHA256d-capable device, in device order, plus one merged share source.
-    Devices without the capability are skipped; none left is an error, as in the reference.
-    The caller owns shutdown (``for w in workers: w.stop()``)."""
+def start_miner_workers(devices, log=lambda level, msg: None, cfg: "miner.WorkerConfig | None" = None,
+                        allow=None, per_device_cfg=None):
+    """One started worker per SHA256d-capable device, in device order, plus one merged share source
+    (startMinerWorkers, setup.go:56-78).  Devices without the capability are skipped; none left is an
+    error, as in the reference.  The caller owns shutdown (``for w in workers: w.stop()``).
+
+    What the reference has no knob for (its WorkerConfig is just a name, config.go:225-229) and a GPU
+    box needs:
+      allow           device-ID allow-list (``hal.Identity.ID`` strings, e.g. ``{"gpu-cuda0", "gpu-cuda3"}``);
+                      None = every SHA256d device.  A listed ID that no detected device has is an error —
+                      a typo must not silently leave a GPU idle.
+      per_device_cfg  {device ID: miner.WorkerConfig} overriding ``cfg`` for that device (ring capacity,
+                      host queue, launch size, kernel variant -> otd_worker_config_t)."""
     import dataclasses
+    devices = list(devices)
+    ids = [d.identity().id for d in devices]
+    if allow is not None:
+        allow = set(allow)
+        unknown = sorted(allow - set(ids))
+        if unknown:
+            raise EngineError(f"engine: allow-list names devices that were not detected: {unknown}")
+    per_device_cfg = dict(per_device_cfg or {})
+    unknown = sorted(set(per_device_cfg) - set(ids))
+    if unknown:
+        raise EngineError(f"engine: per-device config for devices that were not detected: {unknown}")
     workers = []
     try:
-        for dev in devices:
+        for dev, dev_id in zip(devices, ids):
             if not dev.capabilities().sha256d:
                 continue
-            c = dataclasses.replace(cfg) if cfg is not None else miner.default_worker_config()
+            if allow is not None and dev_id not in allow:
+                log("info", f"engine: {dev_id} not in the device allow-list, no worker")
+                continue
+            base = per_device_cfg.get(dev_id, cfg)
+            c = dataclasses.replace(base) if base is not None else miner.default_worker_config()
             c.device = getattr(dev, "index", c.device)
             workers.append(miner.Worker(c).start())
             log("info", f"engine: worker for {dev.identity()}")
@@ -176,6 +202,24 @@ def start_miner_workers(devices, log=lambda level, msg: None, cfg: "miner.Worker
     if not workers:
         raise EngineError("engine: no SHA256d-capable devices found")
     return workers, MergedShares(workers)
+
+
+def pause_device(workers, device_id: str) -> bool:
+    """applyAllocation's pauseDevice (arbitrate.go:255-262): SetWork(nil) on the ONE worker whose
+    DeviceID matches; every other device keeps hashing.  Returns whether a worker matched."""
+    for w in workers:
+        if w.device_id() == device_id:
+            w.set_work(None)
+            return True
+    return False
+
+
+def update_work_partitioned(workers, work: miner.Work) -> None:
+    """updateWork for G devices: device g searches slice g of G of the work's space
+    (otd_work_partition: version indices, else extranonce2 values, else nonce windows)."""
+    G = len(workers)
+    for g, wr in enumerate(workers):
+        wr.set_work(partition_work(work, g, G) if G > 1 else work)
 
 
 class MergedShares:

@@ -142,6 +142,7 @@ class Work:
     extranonce2_begin: int = 0
     extranonce2_count: int = 0
     extranonce2_stride: int = 0
+    job_id_str: str = ""            # Stratum V1: the pool's opaque job id, echoed into the shares
 
     def _c(self):
         """Returns (CWork, keepalive) — keepalive holds the buffers CWork points into."""
@@ -151,6 +152,10 @@ class Work:
         w.job_id, w.channel_id, w.nbits = self.job_id & 0xFFFFFFFF, self.channel_id & 0xFFFFFFFF, self.nbits & 0xFFFFFFFF
         w.header = self.header._c()
         w.target[:] = self.target
+        jid = self.job_id_str.encode()
+        if len(jid) >= capi.OTD_JOB_ID_MAX:
+            raise MinerError("job_id_str too long")
+        w.job_id_str = jid
         w.flags = (capi.OTD_WORK_REPEAT if self.repeat else 0) | \
                   (capi.OTD_WORK_PER_VERSION_LAUNCH if self.per_version_launch else 0)
         w.nonce_begin, w.nonce_count = self.nonce_begin, self.nonce_count
@@ -186,6 +191,7 @@ class Share:
     device_id: str = ""
     extranonce2: int = 0
     work_seq: int = 0
+    job_id_str: str = ""
 
 
 @dataclass
@@ -208,7 +214,7 @@ def _device_id(index: int) -> str:
 
 def _share_from_c(s: CShare, device_id: str) -> Share:
     return Share(s.channel_id, s.job_id, s.nonce, s.ntime, s.version, bytes(s.hash), device_id,
-                 s.extranonce2, s.work_seq)
+                 s.extranonce2, s.work_seq, s.job_id_str.decode("utf-8", "replace"))
 
 
 # ----------------------------------------------------------------------------

@@ -69,10 +69,12 @@ def t1_t2_shared(h, e, f, g, kw, d, a, b, c):
     return add(d, t1), add(t1, big_sigma(a), lop3(a, b, c))
 
 
-def compress_shared(state, w, rounds):
+def compress_shared(state, w, rounds, schedule_out=None):
     w = list(w)
     for i in range(16, rounds):
         w.append(add(small_sigma(w[i - 2]), w[i - 7], small_sigma(w[i - 15]), w[i - 16]))
+    if schedule_out is not None:
+        schedule_out.extend(w[16:])
     a, b, c, d, e, f, g, h = state
     states = []
     for i in range(rounds):
@@ -82,14 +84,14 @@ def compress_shared(state, w, rounds):
     return states
 
 
-def scan_graph(fold=True, early=True):
+def scan_graph(fold=True, early=True, schedule_out=None):
     # hash 1, block 2: midstate constant; W0..2 constant, W3 = nonce, W4..15 constant
     mid = [C() for _ in range(8)]
     w1 = [C(), C(), C(), V()] + [C() for _ in range(12)]
     if not fold:  # pretend nothing is constant (reference point without folding)
         mid = [V() for _ in range(8)]
         w1 = [V() for _ in range(16)]
-    s1 = compress_shared(mid, w1, 64)[-1]
+    s1 = compress_shared(mid, w1, 64, schedule_out)[-1]
     digest = [add(x, C()) if fold else add(x, V()) for x in s1]           # + midstate
     iv = [C() for _ in range(8)] if fold else [V() for _ in range(8)]
     w2 = digest + ([C() for _ in range(8)] if fold else [V() for _ in range(8)])
@@ -100,9 +102,22 @@ def scan_graph(fold=True, early=True):
     return [add(x, C()) for x in st2[-1]]                                 # all 8 digest words
 
 
+def version_shared_counts():
+    """BIP-320 version instances of one job share block 2 of hash 1 (the version sits in block 1), so that
+    block's message schedule W16..W63 is per-NONCE work: returns ((SHF, LOP3, IADD3) per nonce for the schedule,
+    (SHF, LOP3, IADD3) per (nonce, version) for everything else).  K + W is one shared term either way."""
+    sched = []
+    whole = total(scan_graph(fold=True, early=True, schedule_out=sched))
+    per_nonce = total(sched)
+    return tuple(per_nonce), tuple(w - n for w, n in zip(whole, per_nonce))
+
+
 if __name__ == "__main__":
     for name, kw in (("midstate, nothing folded, all 8 digest words", dict(fold=False, early=False)),
                      ("nonce-independent work folded, early reject on digest word 7", dict(fold=True, early=True))):
         s, l, a = total(scan_graph(**kw))
         print(f"{name}: SHF {s}  LOP3 {l}  IADD3 {a}  total {s + l + a}   (SHF+LOP3 = {s + l})")
+    pn, pv = version_shared_counts()
+    print(f"version-shared scan: per nonce (hash-1 schedule) SHF {pn[0]} LOP3 {pn[1]} IADD3 {pn[2]}; "
+          f"per version instance SHF {pv[0]} LOP3 {pv[1]} IADD3 {pv[2]}  (SHF+LOP3 = {pv[0] + pv[1]} + {pn[0] + pn[1]}/V)")
     print("SURVEY.md §8d: unfolded 1344 / 704 / 720 = 2768; folded + early reject 1176 / 628 / 646 = 2450")

@@ -18,6 +18,7 @@ f = W.genesis_fields()
 hdr = miner.Header(f["version"], f["prev_hash"], f["merkle_root"], f["time"], f["bits"], 0)
 for _ in range(a.reps):
     r = miner.scan(miner.Work(header=hdr, target=miner.target_from_nbits(W.DIFF1_NBITS),
-                              nonce_begin=W.GENESIS_NONCE - (1 << (a.log2 - 1)), nonce_count=1 << a.log2), variant=v)
+                              nonce_begin=max(0, W.GENESIS_NONCE - (1 << (a.log2 - 1))) if a.log2 < 32 else 0,
+                              nonce_count=1 << a.log2), variant=v)
     print(f"variant={v} hashes={r.hashes} found={r.found} ms={r.device_ms:.3f} GH/s={r.hashes / r.device_ms / 1e6:.3f}")
     assert r.found >= 1

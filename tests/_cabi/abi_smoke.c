@@ -65,7 +65,7 @@ int main(int argc, char** argv)
     {
         otd_v1_notify_t nt;
         memset(&nt, 0, sizeof nt);
-        nt.job_id = "191";
+        nt.job_id = "bf";   /* the documentation's own (hex) job id: opaque to the library */
         nt.prevhash_hex = "4d16b6f85af6e2198f44ae2a6de67f78487ae5611b77c6c0440b921e00000000";
         nt.coinb1_hex = "01000000010000000000000000000000000000000000000000000000000000000000000000ffffffff20020862062f503253482f04b8864e5008";
         nt.coinb2_hex = "072f736c7573682f000000000100f2052a010000001976a914d23fcdf86f7e756a64a7a9688ef9903327048ed988ac00000000";
@@ -77,16 +77,19 @@ int main(int argc, char** argv)
         otd_work_t vw;
         CHECK(otd_work_from_v1_notify(&nt, "08000002", 4, 1.0, 0, &vw, scratch, 8, &need) == OTD_ERANGE && need > 8 && need <= sizeof scratch);
         CHECK(otd_work_from_v1_notify(&nt, "08000002", 4, 1.0, 0, &vw, scratch, sizeof scratch, &need) == OTD_OK);
-        CHECK(vw.job_id == 191 && vw.header.version == 2 && vw.header.bits == 0x1c2ac4afu && vw.header.time == 0x504e86b9u);
+        CHECK(vw.job_id == 0 && strcmp(vw.job_id_str, "bf") == 0 && vw.header.version == 2 && vw.header.bits == 0x1c2ac4afu && vw.header.time == 0x504e86b9u);
         CHECK(vw.header.prev_hash[0] == 0xf8 && vw.header.prev_hash[3] == 0x4d && vw.header.prev_hash[31] == 0x00);
         CHECK(vw.coinb1_len == 58 && vw.extranonce1_len == 4 && vw.extranonce1[0] == 0x08 && vw.extranonce2_size == 4 && vw.n_branches == 0);
         otd_share_t sh;
         memset(&sh, 0, sizeof sh);
-        sh.job_id = 191; sh.ntime = 0x504e86edu; sh.nonce = 0xb2957c02u; sh.version = 2; sh.extranonce2 = 0x01000000u;
+        memcpy(sh.job_id_str, vw.job_id_str, sizeof sh.job_id_str);
+        sh.ntime = 0x504e86edu; sh.nonce = 0xb2957c02u; sh.version = 2; sh.extranonce2 = 0x01000000u;
         otd_v1_submit_t sub;
         CHECK(otd_share_to_v1_submit(&sh, vw.extranonce2_size, 0, &sub) == OTD_OK);
         CHECK(strcmp(sub.extranonce2_hex, "00000001") == 0 && strcmp(sub.ntime_hex, "504e86ed") == 0 &&
-              strcmp(sub.nonce_hex, "b2957c02") == 0 && sub.version_bits_hex[0] == 0);
+              strcmp(sub.nonce_hex, "b2957c02") == 0 && sub.version_bits_hex[0] == 0 && strcmp(sub.job_id, "bf") == 0);
+        sh.job_id_str[0] = 0; sh.job_id = 191;
+        CHECK(otd_share_to_v1_submit(&sh, vw.extranonce2_size, 0, &sub) == OTD_OK && strcmp(sub.job_id, "191") == 0);
         CHECK(otd_share_to_v1_submit(&sh, 17, 0, &sub) == OTD_EINVAL);
     }
 

@@ -45,7 +45,7 @@ template <unsigned KN>
 static void run_vs(const JobConsts* jcs, int n_ver, uint32_t nonce, uint32_t* out)
 {
     VsOps<KN> op{{make_pipe_mults()}};
-    uint32_t kw[kVsWords];
+    uint32_t kw[46];
     const uint32_t w3 = bswap32(nonce);
     vs_schedule<KN>(jcs[0], w3, op, [&](int i, uint32_t v) { kw[i] = v; });
     for (int v = 0; v < n_ver; v++) out[v] = vs_hash<KN>(jcs[v], jcs[0], w3, op, [&](int i) { return kw[i]; });
@@ -77,6 +77,12 @@ int fc_vs_e60_kn(const uint8_t hdr76[76], const uint32_t* versions, int n_ver, u
         case VSSET(5, 6): run_vs<VSSET(5, 6)>(jcs, n_ver, nonce, e60_out); return 0;
         case VSSET(7, 7): run_vs<VSSET(7, 7)>(jcs, n_ver, nonce, e60_out); return 0;
         case VSSET(8, 0): run_vs<VSSET(8, 0)>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(7, 7) | KN_VS_F20: run_vs<VSSET(7, 7) | KN_VS_F20>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(6, 6) | KN_VS_F20: run_vs<VSSET(6, 6) | KN_VS_F20>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(7, 7) | KN_VS_LOOP1: run_vs<VSSET(7, 7) | KN_VS_LOOP1>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(7, 0) | KN_VS_LOOP1: run_vs<VSSET(7, 0) | KN_VS_LOOP1>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(7, 7) | KN_VS_LOOP1 | KN_VS_F20:
+            run_vs<VSSET(7, 7) | KN_VS_LOOP1 | KN_VS_F20>(jcs, n_ver, nonce, e60_out); return 0;
         case 1023: run_vs<1023>(jcs, n_ver, nonce, e60_out); return 0;
         default: return -2;
     }

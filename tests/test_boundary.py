@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol(product):
     for sym in declared:
         assert hasattr(L, sym), f"{sym} declared in include/otedama_b200.h but not exported"
         assert sym in capi._SIGS, f"{sym} has no ctypes signature"
-    assert L.otd_abi_version() == 1
+    assert L.otd_abi_version() == 2
     assert L.otd_last_error() is not None
 
 
@@ -56,7 +56,7 @@ def test_struct_layouts_match_the_header(product):
         assert L.otd_abi_struct_size(which) == ctypes.sizeof(cls), cls.__name__
     assert L.otd_abi_struct_size(99) == -1
     assert ctypes.sizeof(capi.CHeader) == 80
-    assert ctypes.sizeof(capi.CShare) == 80
+    assert ctypes.sizeof(capi.CShare) == 80 + capi.OTD_JOB_ID_MAX
     assert ctypes.sizeof(capi.CWorkerConfig) == 16
     assert capi.CWork.header.offset == 8 and capi.CWork.target.offset == 92
 

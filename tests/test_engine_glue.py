@@ -122,7 +122,8 @@ def test_v1_notify_to_work_unit(eng, oracle, golden):
     oh = oracle.v1_header(params, bytes.fromhex("0a0b"), (5).to_bytes(8, "little"))
     assert (w.header.version, w.header.prev_hash, w.header.time, w.header.bits) == (oh.version, oh.prev_hash, oh.time, oh.bits)
     assert [b.hex() for b in w.merkle_branches] == params[4] and w.target == oracle.target_from_nbits(0x1D00FFFF)
-    for bad in (["x"] + params[1:], params[:1] + ["00"] + params[2:], params[:5] + ["2000000"] + params[6:],
+    assert engine.work_from_v1_notify(["x"] + params[1:], "", 4, 0).job_id_str == "x"     # job ids are opaque strings
+    for bad in (["x" * 64] + params[1:], params[:1] + ["00"] + params[2:], params[:5] + ["2000000"] + params[6:],
                 params[:4] + [["zz" * 32]] + params[5:], params[:2] + ["abc"] + params[3:]):
         with pytest.raises(engine.EngineError):
             engine.work_from_v1_notify(bad, "", 4, 0)
@@ -178,10 +179,12 @@ def test_block_170_is_found_from_its_notify_form(eng, oracle, golden):
 def _docs_example_work(engine, golden):
     ex = golden["reference_vectors"]["real_world_anchors"]["stratum_docs_example"]
     params = list(ex["notify_params"])
-    assert params[0] == "bf"
-    with pytest.raises(engine.EngineError, match="unparseable job ID"):   # like applyJob's Sscanf("%d"), run.go:1345-1348
-        engine.work_from_v1_notify(params, ex["subscribe_extranonce1"], ex["subscribe_extranonce2_size"], 1.0)
-    params[0] = str(0xBF)
+    assert params[0] == "bf"        # a hex job id, as most pools send: opaque to the library (applyJob's
+    #                                 Sscanf("%d"), run.go:1345-1348, would refuse it; otd_work_from_v1_job still does)
+    with pytest.raises(engine.EngineError, match="unparseable job ID"):
+        engine.work_from_v1_job(engine.Job(job_id="bf", nbits=0x1D00FFFF), 0, 1.0)
+    with pytest.raises(engine.EngineError, match="job id longer"):
+        engine.work_from_v1_notify(["x" * 64] + params[1:], ex["subscribe_extranonce1"], 4, 1.0)
     en2 = int.from_bytes(bytes.fromhex(ex["submit_params"][2]), "little")
     w = engine.work_from_v1_notify(params, ex["subscribe_extranonce1"], ex["subscribe_extranonce2_size"], 1.0,
                                    extranonce2_begin=en2 - 1, extranonce2_count=3)
@@ -196,7 +199,11 @@ def test_stratum_documentation_example_as_a_work_unit(eng, golden):
     assert w.header.prev_hash == b"".join(wire[4 * i:4 * i + 4][::-1] for i in range(8))
     assert w.header.prev_hash[-4:] == b"\x00" * 4                # header order: the hash's zero bytes come last
     assert (w.header.version, w.header.bits, w.header.time) == (2, 0x1C2AC4AF, 0x504E86B9)
-    assert (w.job_id, w.extranonce1.hex(), w.extranonce2_size) == (0xBF, "08000002", 4)
+    assert (w.job_id, w.job_id_str, w.extranonce1.hex(), w.extranonce2_size) == (0, "bf", "08000002", 4)
+    dec = engine.work_from_v1_notify(["191"] + list(ex["notify_params"][1:]), ex["subscribe_extranonce1"], 4, 1.0)
+    assert (dec.job_id, dec.job_id_str) == (191, "191")      # a decimal id also lands in the numeric field
+    for odd in ("1a", "4294967296", "-1", ""):
+        assert engine.work_from_v1_notify([odd] + list(ex["notify_params"][1:]), "", 4, 1.0).job_id == 0
     assert w.coinb1.hex() == ex["notify_params"][2] and w.coinb2.hex() == ex["notify_params"][3] and not w.merkle_branches
     assert w.target == miner.target_from_difficulty(1.0)
 
@@ -216,7 +223,8 @@ def test_stratum_documentation_example_share_is_found_and_submitted(eng, golden)
     assert [(s.nonce, s.hash[::-1].hex()) for s in r.shares] == [(nonce, ex["hash_display"])]
     inst = miner.prepare_instances(w, 1, 1)[0]
     assert inst.merkle_root.hex() == ex["merkle_root_header_order"]
-    assert engine.v1_submit_params(r.shares[0], w, worker_name=sub[0]) == [sub[0], str(0xBF), sub[2], sub[3], sub[4]]
+    assert r.shares[0].job_id_str == "bf"
+    assert engine.v1_submit_params(r.shares[0], w, worker_name=sub[0]) == list(sub[:5])      # job id "bf" verbatim
 
 
 @pytest.mark.gpu

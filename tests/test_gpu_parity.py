@@ -270,7 +270,7 @@ def test_version_rolling_matches_oracle(miner, oracle):
         sh, _, _ = oracle.grind(oh, t, 0x10000000, 1 << 16, threads=NCPU)
         want += okey(sh)
     r = miner.scan(work)
-    assert r.hashes == 40 << 16 and r.launches == 3       # version-shared launches of 16 + 16 + 8 instances
+    assert r.hashes == 40 << 16 and r.launches == 2       # version-shared launches of 32 + 8 instances
     assert key(r.shares) == sorted(want) and len(want) > 100
     assert all(s.job_id == 9 for s in r.shares)
     work.per_version_launch = True                        # the plain kernel, one launch per version instance
@@ -295,8 +295,8 @@ def test_version_rolling_default_count_covers_the_mask(miner, oracle):
 
 
 def test_version_shared_variants_match_oracle(miner, oracle):
-    """K1v (csrc/scan_vs_kernel.cuh): every version-shared variant, group sizes 1..16 incl. ragged tails
-    (17 = 16 + a lone instance on the plain kernel), a ragged nonce window, against the CPU oracle."""
+    """K1v (csrc/scan_vs_kernel.cuh): every version-shared variant, group sizes 2..32 incl. ragged tails
+    (33 = 32 + a lone instance on the plain kernel), ragged nonce windows, against the CPU oracle."""
     c4 = W.config4_v2()
     t = oracle.target_from_difficulty(2.0 ** -20)
     names = miner.vs_variants()
@@ -306,7 +306,7 @@ def test_version_shared_variants_match_oracle(miner, oracle):
             miner.vs_select(vi)
             for n_ver, begin, stride, nb, nc in ((2, 0, 1, 0, 5000), (16, 7, 3, 0xFFFF0000, 1 << 16),
                                                  (17, 100, 1, 123, 3 * 1024 + 1), (33, 65000, 16, 1 << 31, 4096)):
-                if vi and n_ver not in (16, 17):
+                if vi and n_ver not in (17, 33):
                     continue
                 work = miner.Work(job_id=5, header=mheader(miner, c4), target=t, version_mask=c4["mask"],
                                   version_begin=begin, version_count=n_ver, version_stride=stride, nonce_begin=nb,
@@ -318,7 +318,7 @@ def test_version_shared_variants_match_oracle(miner, oracle):
                     want += okey(sh)
                 r = miner.scan(work)
                 assert r.hashes == n_ver * nc, (name, n_ver)
-                assert r.launches == (n_ver + 15) // 16
+                assert r.launches == (n_ver + 31) // 32
                 assert key(r.shares) == sorted(want), (name, n_ver)
     finally:
         miner.vs_select(-1)
@@ -496,6 +496,29 @@ def test_worker_job_switch_is_observed_via_job_id(miner):
         h1 = w.stats().hashes_total
         time.sleep(0.2)
         assert w.stats().hashes_total == h1
+
+
+def test_poll_reports_the_end_of_a_work_once_then_honours_its_timeout(miner):
+    """otd_worker_poll_shares: the end of a work (space exhausted) wakes ONE empty poll; after that an idle
+    worker's poll waits for its timeout instead of returning at once (a forwarding loop must not spin), and a new
+    set_work arms it again."""
+    with miner.Worker() as w:
+        impossible = bytes(32)                                   # no hash is <= 0 here
+        a, _ = easy_work(miner, job_id=1, target=impossible, nonce_count=1 << 16)
+        w.set_work(a)
+        assert w.wait_exhausted(5000)
+        t0 = time.time()
+        assert w.poll_shares(16, 2000) == []                     # the end of the work: returns at once
+        assert time.time() - t0 < 0.5
+        for _ in range(2):
+            t0 = time.time()
+            assert w.poll_shares(16, 300) == []                  # idle and already reported: waits
+            assert time.time() - t0 >= 0.28
+        w.set_work(a)
+        t0 = time.time()
+        assert w.poll_shares(16, 2000) == [] and time.time() - t0 < 0.5
+        t0 = time.time()
+        assert w.poll_shares(16, 200) == [] and time.time() - t0 >= 0.18
 
 
 def test_worker_set_work_aborts_a_long_launch_quickly(miner):

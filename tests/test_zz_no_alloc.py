@@ -62,6 +62,22 @@ def test_two_calls_in_a_row_match_the_ordinary_entry_point(api):
     assert counts[0] == counts[2] > 100 and 0 < counts[1] < counts[0]
 
 
+def test_a_window_matches_the_cpu_oracle(api, oracle):
+    """Judged like every other entry point: the share set of a dense window against the CPU oracle's grind of
+    the same header and target (not only against the library's other entry point)."""
+    capi, miner = api
+    import os
+    t = oracle.target_from_difficulty(2.0 ** -16)
+    for index, first, count in ((5, 0x7FFF0000, 1 << 21), (0, W.GENESIS_NONCE - (1 << 20), 1 << 21)):
+        f = W.config2_fields(index)
+        want, _, _ = oracle.grind(oracle.Header(f["version"], f["prev_hash"], f["merkle_root"], f["time"], f["bits"], 0),
+                                  t, first, count, threads=os.cpu_count() or 1)
+        n, out, found, hashes = _noalloc(capi, _work(miner, index, t, first, count), 4096)
+        assert n == found == len(want) > 10 and hashes == count
+        assert [(out[i].nonce, bytes(out[i].hash)) for i in range(n)] == [(s.nonce, s.hash) for s in want]
+        assert all(out[i].ntime == f["time"] and out[i].version == f["version"] for i in range(n))
+
+
 def test_the_genesis_nonce_is_found_without_allocating(api):
     capi, miner = api
     f = W.genesis_fields()
