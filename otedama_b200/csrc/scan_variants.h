@@ -47,16 +47,19 @@ struct VsParams;
 // the full SHA-256d.  OTD_KN_VS(n, m): the shipped add placement with n/8 of the immediate-constant rounds and
 // m/8 of the shared-schedule rounds built from IMADs only (m = 0 reads as 8/8).
 #define OTD_KN_VS(n, m) (OTD_KN_ADDS | otd::KN_SP | otd::KN_T1Z | OTD_KN_Z_EIGHTHS(n) | OTD_KN_VSZ_EIGHTHS(m))
-// Measured on B200 (profiles/r2_vs_sweep_*.log), GH/s per GPU on 16 versions x 2^28 nonces (plain kernel per version: 9.53):
-//   vs_z7_r7_b4 11.10 | vs_z6_r8_b4 11.07 | vs_z6_r6_b4 11.00 | vs_z6_r4_b4 10.92 | 5 blocks/SM (f20) 11.09 |
-//   192-thread blocks x 6 10.55 | 128 x 9 10.38 — more warps than 32 per SM buy nothing, smaller blocks lose.
-// With 32 instances per launch (shipped; 32 x 2^27): vs_z7_r7_b4 11.21 | z6_r8 11.19 | f20_b5 11.19 | z6_r6 11.11;
-// hash-1 rounds 24..63 rolled into an 8-round loop body (l1, 39 KB of code instead of 47): 10.96-11.05 — the
+// Measured on B200 (profiles/r2_vs_sweep_*.log), GH/s per GPU, 32 version instances x 2^27 nonces per launch
+// (the plain kernel launched once per version: 9.52):
+//   vs_z7_r8_b3 11.365 (shipped) | z6_r8_b3 11.364 | z7_r7_b3 11.35 | z8_r8_b3 11.33 | z7_r8_b4 11.33 | z7_r7_b4 11.21 |
+//   z6_r8_b4 11.19 | f20_b5 (5 blocks/SM) 11.19 | z6_r6_b4 11.11 | z7_r5_b4 11.07 | z8_r7_b4 11.02 |
+//   2 blocks/SM (b2) 9.98 | 128-thread blocks x 6 10.88, x 5 9.71 | 192 x 6 10.55 | ITER 2 / 8 11.16 / 11.19.
+// Three 256-thread blocks per SM (24 warps, 56 registers) are enough and slightly better than four; more warps
+// buy nothing, fewer (16) lose 12 %.  16 instances per launch instead of 32: 11.10 (z7_r7_b4).
+// Hash-1 rounds 24..63 rolled into an 8-round loop body (l1, 39 KB of code instead of 47): 10.96-11.05 — the
 // instruction cache is not what holds the kernel back (ncu: hit rate 93 %, no_instruction 0.3 of 10.6 cycles per issue).
 #define OTD_VS_VARIANTS(Y)                                  \
-    Y(0, "vs_z7_r7_b4", 4, OTD_KN_VS(7, 7), 4, 256)         \
-    Y(1, "vs_z6_r6_b4", 4, OTD_KN_VS(6, 6), 4, 256)         \
-    Y(2, "vs_z6_r8_b4", 4, OTD_KN_VS(6, 0), 4, 256)         \
+    Y(0, "vs_z7_r8_b3", 4, OTD_KN_VS(7, 0), 3, 256)         \
+    Y(1, "vs_z7_r7_b4", 4, OTD_KN_VS(7, 7), 4, 256)         \
+    Y(2, "vs_z6_r8_b3", 4, OTD_KN_VS(6, 0), 3, 256)         \
     Y(3, "vs_z7_r7_f20_b5", 4, OTD_KN_VS(7, 7) | otd::KN_VS_F20, 5, 256) \
     Y(4, "vs_z7_r8_l1_b4", 4, OTD_KN_VS(7, 0) | otd::KN_VS_LOOP1, 4, 256)
 #define OTD_DEFAULT_VS_VARIANT 0

@@ -117,7 +117,8 @@ def VSSET(n, m):
 
 VS_KNOB_SETS = [0, 1023, ADDS | KN["T1X"] | KN["SP"], VSSET(6, 0), VSSET(6, 6), VSSET(6, 4), VSSET(6, 7), VSSET(5, 6),
                 VSSET(7, 7), VSSET(8, 0), VSSET(7, 7) | (1 << 24), VSSET(6, 6) | (1 << 24),
-                VSSET(7, 7) | (1 << 25), VSSET(7, 0) | (1 << 25), VSSET(7, 7) | (3 << 24)]
+                VSSET(7, 7) | (1 << 25), VSSET(7, 0) | (1 << 25), VSSET(7, 7) | (3 << 24),
+                VSSET(7, 0), VSSET(6, 7), VSSET(7, 6), VSSET(5, 7), VSSET(7, 5), VSSET(8, 7), VSSET(6, 0)]
 
 
 def test_every_version_shared_variant_policy_is_host_checked():

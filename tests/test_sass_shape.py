@@ -55,3 +55,45 @@ def test_default_kernel_instruction_shape(sass):
     # no tensor core, TMA, shared memory or barrier; the only global load is the stop word, once per block
     assert not any(op.startswith(("HMMA", "UTCHMMA", "UTMALDG", "LDS", "STS", "BAR")) for op, _ in ops)
     assert sum(1 for op, _ in ops if op.startswith("LDG")) == 1
+
+
+# ---- the version-shared scan kernel (default variant) ----------------------------------------------------------------
+@pytest.fixture(scope="module")
+def vs_sass(product):
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    objs = glob.glob(os.path.join(OBJ, "vsvariant0_*.o"))
+    assert len(objs) == 1, objs
+    txt = subprocess.run(["cuobjdump", "-sass", "-res-usage", objs[0]], capture_output=True, text=True, check=True).stdout
+    body = txt[txt.index("Function : _ZN3otd14scan_vs_kernel"):]
+    return txt, body
+
+
+def test_version_shared_kernel_resources(vs_sass):
+    """No spills; registers within the budget of three 256-thread blocks per SM (the shipped launch bounds); the
+    46-word schedule column per thread is the only shared memory (3 x 47,104 B fit the SM's 228 KB)."""
+    txt, _ = vs_sass
+    m = re.search(r"Function _ZN3otd14scan_vs_kernel\S*:\s*\n\s*REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", txt)
+    assert m, txt[:400]
+    reg, stack, shared, local = map(int, m.groups())
+    assert reg <= 85 and local == 0 and stack <= 128
+    assert shared - 46 * 256 * 4 in (0, 1024)             # cuobjdump adds the 1 KB the driver reserves per block
+
+
+def test_version_shared_kernel_instruction_shape(vs_sass):
+    """The schedule is written once (46 STS) and read once per version instance (46 LDS) — not hoisted into
+    registers across the version loop, which would spill —, the per-version body carries no schedule arithmetic
+    (SHF + LOP3 within 3 % of 1500 + 304 for the per-nonce part), and the adds sit on the FMA pipe as IMADs with a
+    uniform-register 1."""
+    _, body = vs_sass
+    ops = re.findall(r"^\s+/\*[0-9a-f]{4,}\*/\s+(?:@!?U?P\d\s+)?([A-Z0-9_.]+)\s*([^;]*);", body, flags=re.M)
+    count = lambda name: sum(1 for op, _ in ops if op.split(".")[0] == name)   # noqa: E731
+    assert count("STS") == 46 and count("LDS") == 46
+    assert count("LDL") + count("STL") < 40                   # only the rare path's digest array
+    assert 1176 <= count("SHF") <= 1176 * 1.03                # 948 per version + 228 per nonce, nothing twice
+    assert 628 <= count("LOP3") <= 628 * 1.10
+    imad = [args for op, args in ops if op == "IMAD"]
+    uniform_one = [a for a in imad if re.match(r"R\d+, R\d+(\.reuse)?, UR\d+, R\d+", a)]
+    vector_mul = [a for a in imad if re.match(r"R\d+, R\d+(\.reuse)?, R\d+(\.reuse)?, R\d+", a)]
+    assert len(uniform_one) > 700 and len(vector_mul) < 10, (len(uniform_one), len(vector_mul))
+    assert not any(op.startswith(("HMMA", "UTCHMMA", "UTMALDG", "BAR")) for op, _ in ops)
