@@ -89,7 +89,7 @@ def test_version_shared_kernel_instruction_shape(vs_sass):
     ops = re.findall(r"^\s+/\*[0-9a-f]{4,}\*/\s+(?:@!?U?P\d\s+)?([A-Z0-9_.]+)\s*([^;]*);", body, flags=re.M)
     count = lambda name: sum(1 for op, _ in ops if op.split(".")[0] == name)   # noqa: E731
     assert count("STS") == 46 and count("LDS") == 46
-    assert count("LDL") + count("STL") < 40                   # only the rare path's digest array
+    assert count("LDL") + count("STL") < 64                   # only the rare path's digest array
     assert 1176 <= count("SHF") <= 1176 * 1.03                # 948 per version + 228 per nonce, nothing twice
     assert 628 <= count("LOP3") <= 628 * 1.10
     imad = [args for op, args in ops if op == "IMAD"]
