@@ -12,6 +12,7 @@ import "C"
 import (
 	"context"
 	"fmt"
+	"runtime"
 )
 
 type cudaDevice struct {
@@ -20,17 +21,25 @@ type cudaDevice struct {
 	caps  Capabilities
 }
 
-func (d *cudaDevice) Identity() Identity         { return d.id }
-func (d *cudaDevice) Capabilities() Capabilities { return d.caps }
+func (d *cudaDevice) Identity() Identity             { return d.id }
+func (d *cudaDevice) Capabilities() Capabilities     { return d.caps }
 func (d *cudaDevice) Shutdown(context.Context) error { return nil } // idempotent; workers own device state
-func (d *cudaDevice) Index() int                  { return d.index }
+func (d *cudaDevice) Index() int                     { return d.index }
 
-// CUDADriver implements hal.Driver (internal/hal/device.go:182-198).
+// CUDAIndexed is implemented by devices of this driver: the engine needs the CUDA ordinal to open a worker.
+type CUDAIndexed interface{ Index() int }
+
+// CUDADriver implements hal.Driver (internal/hal/device.go:182-198). It is registered next to
+// GPULinuxDriver in engine.detectDevices (setup.go:29-36); the sysfs driver keeps reporting SHA256d:false
+// for the same boards (gpu_linux.go:20-31), this one reports what the library's kernels can do.
 type CUDADriver struct{}
 
 func (CUDADriver) Name() string { return "cuda" }
 
 func (CUDADriver) Enumerate(ctx context.Context) ([]Device, error) {
+	// otd_last_error() is thread-local: keep the failing call and the read of its message on one OS thread
+	runtime.LockOSThread()
+	defer runtime.UnlockOSThread()
 	n := int(C.otd_device_count())
 	if n < 0 {
 		return nil, fmt.Errorf("hal/cuda: %s", C.GoString(C.otd_last_error()))
@@ -42,7 +51,7 @@ func (CUDADriver) Enumerate(ctx context.Context) ([]Device, error) {
 		}
 		var info C.otd_device_info_t
 		if C.otd_device_info(C.int(i), &info) != 0 {
-			continue
+			continue // one bad board does not hide the others (registry.go:180-190 logs per driver)
 		}
 		devs = append(devs, &cudaDevice{
 			index: i,

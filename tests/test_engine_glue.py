@@ -427,3 +427,132 @@ def test_pool_side_check_of_submitted_fields(eng, oracle):
         version = (c3["version"] & ~mask) | (int(vbits_hex, 16) & mask)
         h = oracle.Header(version, c3["prev_hash"], root, int(ntime_hex, 16), c3["bits"], int(nonce_hex, 16))
         assert oracle.hash_header(h) == s.hash and oracle.less_or_equal(s.hash, target)
+
+
+@pytest.mark.gpu
+def test_notify_to_submit_round_trip_with_rolled_versions(eng, oracle):
+    """The whole V1 path a pool sees, end to end through the worker: mining.notify params with
+    a HEX job id -> otd_work_from_v1_notify -> extranonce2 x BIP-320 version x nonce on the device -> share ->
+    mining.submit fields -> the pool's own re-hash from nothing but the job it sent and the submitted strings."""
+    from otedama_b200 import workloads as W
+    engine, miner = eng
+    c3 = W.config3_v1()
+    mask = 0x1FFFE000
+    prev_wire = b"".join(c3["prev_hash"][4 * i:4 * i + 4][::-1] for i in range(8)).hex()
+    notify = ["1f9a", prev_wire, c3["coinb1"].hex(), c3["coinb2"].hex(), [b.hex() for b in c3["branches"]],
+              "%08x" % c3["version"], "%08x" % c3["bits"], "%08x" % c3["time"], True]
+    en1 = c3["extranonce1"].hex()
+    w = engine.work_from_v1_notify(notify, en1, 4, 2.0 ** -16, chan_id=5, extranonce2_begin=0xFFFE, extranonce2_count=3)
+    w.version_mask, w.version_begin, w.version_count = mask, 40, 33           # 32 + a lone instance per extranonce2
+    w.nonce_begin, w.nonce_count = 0xFFFF0000, 1 << 16
+    assert (w.job_id, w.job_id_str) == (0, "1f9a")
+    with miner.Worker() as wk:
+        wk.set_work(w)
+        assert wk.wait_exhausted(30000)
+        got = []
+        while True:
+            part = wk.poll_shares(4096, 0)
+            if not part:
+                break
+            got += part
+    assert len(got) > 50 and {s.extranonce2 for s in got} == {0xFFFE, 0xFFFF, 0x10000}
+    target = oracle.target_from_difficulty(2.0 ** -16)
+    seen_versions = set()
+    for s in got:
+        worker_name, job, en2_hex, ntime_hex, nonce_hex, vbits_hex = engine.v1_submit_params(s, w)
+        assert job == "1f9a" and len(en2_hex) == 8
+        # pool side: everything below comes from `notify`, the subscribe result and the submitted strings
+        coinbase_root = oracle.v1_merkle_root(bytes.fromhex(notify[2]), bytes.fromhex(en1), bytes.fromhex(en2_hex),
+                                              bytes.fromhex(notify[3]), [bytes.fromhex(b) for b in notify[4]])
+        wire = bytes.fromhex(notify[1])
+        prev = b"".join(wire[4 * i:4 * i + 4][::-1] for i in range(8))
+        version = (int(notify[5], 16) & ~mask) | (int(vbits_hex, 16) & mask)
+        h = oracle.Header(version, prev, coinbase_root, int(ntime_hex, 16), int(notify[6], 16), int(nonce_hex, 16))
+        assert oracle.hash_header(h) == s.hash and oracle.less_or_equal(s.hash, target)
+        seen_versions.add(version)
+    assert len(seen_versions) > 20
+
+
+# -- device allow-list, per-device configuration, pause by device id (SURVEY §8f-3) ---------------------------------
+class _FakeCudaDevice:
+    def __init__(self, index, dev_id):
+        self.index, self._id = index, dev_id
+
+    def identity(self):
+        from otedama_b200 import hal
+        return hal.Identity(self._id, hal.FAMILY_GPU, "nvidia", "B200")
+
+    def capabilities(self):
+        from otedama_b200 import hal
+        return hal.Capabilities(sha256d=True, general_compute=True)
+
+
+def test_allow_list_and_per_device_config_reach_the_worker_constructor(eng, monkeypatch):
+    """setup.go:59-77 gives every SHA256d device a worker with default settings; a GPU box needs to leave devices
+    out and to size rings / launches per device.  No GPU needed: the worker constructor is observed."""
+    engine, miner = eng
+    made = []
+
+    class FakeWorker:
+        def __init__(self, cfg):
+            self.cfg = cfg
+            made.append(cfg)
+
+        def start(self):
+            return self
+
+        def stop(self):
+            pass
+
+        def device_id(self):
+            return f"gpu-cuda{self.cfg.device}"
+
+    monkeypatch.setattr(miner, "Worker", FakeWorker)
+    devs = [_FakeCudaDevice(i, f"gpu-cuda{i}") for i in range(4)] + [_NoSha256dDevice()]
+    base = miner.WorkerConfig(ring_capacity=1024, launch_log2=30)
+    special = miner.WorkerConfig(ring_capacity=8192, queue_capacity=16, launch_log2=28, kernel_variant=1)
+    logged = []
+    workers, _ = engine.start_miner_workers(devs, log=lambda lv, m: logged.append(m), cfg=base,
+                                            allow={"gpu-cuda0", "gpu-cuda2", "gpu-cuda3"},
+                                            per_device_cfg={"gpu-cuda2": special})
+    assert [w.cfg.device for w in workers] == [0, 2, 3]                     # gpu-cuda1 filtered, no worker
+    assert any("gpu-cuda1 not in the device allow-list" in m for m in logged)
+    c0, c2, c3 = made
+    assert (c0.ring_capacity, c0.launch_log2, c0.kernel_variant) == (1024, 30, -1)
+    assert (c2.ring_capacity, c2.queue_capacity, c2.launch_log2, c2.kernel_variant, c2.device) == (8192, 16, 28, 1, 2)
+    assert (c3.ring_capacity, c3.launch_log2) == (1024, 30)
+    assert base.device == 0 and special.device == 0                        # the caller's configs are not edited
+    with pytest.raises(engine.EngineError, match="not detected"):
+        engine.start_miner_workers(devs, allow={"gpu-cuda9"})
+    with pytest.raises(engine.EngineError, match="not detected"):
+        engine.start_miner_workers(devs, per_device_cfg={"gpu-cuda7": special})
+    with pytest.raises(engine.EngineError, match="SHA256d"):
+        engine.start_miner_workers(devs, allow=set())                       # everything filtered = nothing to mine on
+
+
+@pytest.mark.gpu
+def test_pause_by_device_id_stops_only_that_worker(eng, oracle):
+    """applyAllocation's pauseDevice (arbitrate.go:255-262): SetWork(nil) on the named device only.  Two workers
+    (two GPUs when the box has them, else both on device 0): the named one stops hashing, the other keeps going."""
+    import time
+    from otedama_b200 import hal, workloads as W
+    engine, miner = eng
+    ndev = len(hal.CudaDriver().enumerate())
+    a = miner.Worker(miner.WorkerConfig(device=0, launch_log2=24)).start()
+    b = miner.Worker(miner.WorkerConfig(device=1 % ndev, launch_log2=24)).start()
+    b.device_id = lambda: "gpu-cuda-second"                                # distinct ids also on a 1-GPU box
+    try:
+        f = W.config2_fields(40)
+        work = miner.Work(header=miner.Header(f["version"], f["prev_hash"], f["merkle_root"], f["time"], f["bits"], 0),
+                          target=bytes(32), repeat=True)
+        engine.update_work_partitioned([a, b], work)
+        time.sleep(0.5)
+        assert a.stats().hashes_total > 0 and b.stats().hashes_total > 0
+        assert engine.pause_device([a, b], "gpu-cuda-second") and not engine.pause_device([a, b], "gpu-cuda9")
+        time.sleep(0.3)
+        hb, ha = b.stats().hashes_total, a.stats().hashes_total
+        time.sleep(0.5)
+        assert b.stats().hashes_total == hb and not b.has_work()          # paused
+        assert a.stats().hashes_total > ha and a.has_work()               # untouched
+    finally:
+        a.stop(); b.stop()
