@@ -24,6 +24,9 @@ ap.add_argument("--gpus", type=int, default=1)
 ap.add_argument("--seconds", type=float, default=600.0)
 ap.add_argument("--interval", type=float, default=10.0)
 ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sustained.csv"))
+ap.add_argument("--versions", type=int, default=0,
+                help="also roll this many BIP-320 versions per extranonce2 value (0 = extranonce2 x nonce only); "
+                     "rolled work goes through the version-shared kernel")
 a = ap.parse_args()
 
 devices = hal.CudaDriver().enumerate()[:a.gpus]
@@ -36,7 +39,8 @@ for g, w in enumerate(workers):
                                                         c3["bits"], 0),
                           nbits=c3["bits"], target=diff1, coinb1=c3["coinb1"], extranonce1=c3["extranonce1"],
                           coinb2=c3["coinb2"], merkle_branches=c3["branches"], extranonce2_size=8,
-                          extranonce2_begin=g, extranonce2_count=1 << 16, extranonce2_stride=G))
+                          extranonce2_begin=g, extranonce2_count=1 << 16, extranonce2_stride=G,
+                          version_mask=W.BIP320_MASK if a.versions else 0, version_count=a.versions))
 
 rows = ["t_s,gpu,ghs_interval,power_w,sm_mhz,temp_c,joules_per_terahash"]
 shares = []
@@ -81,11 +85,12 @@ def ok(s):
 bad = [s for s in shares if not ok(s)]
 hashes = sum(s.hashes_total for s in stats)
 ghs_cols = [float(r.split(",")[2]) for r in rows[1:]]
-summary = {"gpus": G, "seconds": round(dt, 1), "hashes": hashes, "ghs_wall": hashes / dt / 1e9,
+summary = {"gpus": G, "versions_per_extranonce2": a.versions, "one_process": True, "seconds": round(dt, 1), "hashes": hashes, "ghs_wall": hashes / dt / 1e9,
            "ghs_device": hashes / max(1e-9, max(s.device_ms for s in stats) * 1e-3) / 1e9,
            "interval_ghs_min": min(ghs_cols) if ghs_cols else None, "interval_ghs_max": max(ghs_cols) if ghs_cols else None,
            "shares": len(shares), "shares_bad": len(bad), "expected_shares": hashes * (0xFFFF / 2 ** 48),
-           "dropped": sum(s.shares_dropped for s in stats)}
+           "dropped": sum(s.shares_dropped for s in stats),
+           "extrapolated_2p48_sweep_minutes": (1 << 48) / max(1.0, hashes / dt) / 60.0}
 os.makedirs(os.path.dirname(a.out), exist_ok=True)
 with open(a.out, "w") as f:
     f.write("# " + json.dumps(summary) + "\n")

@@ -71,6 +71,16 @@ def test_hash_headers_matches_oracle(miner, oracle, n):
     assert miner.hash_headers([]) == []
 
 
+def test_hash_headers_across_staging_chunks(miner, oracle):
+    """The entry point pipelines chunks of 2^18 headers through two pinned staging slots: ragged multi-chunk
+    batches (1, 2 and 3+ chunks, back to back so slots are reused dirty) against the oracle."""
+    rnd = random.Random(77)
+    for n in ((1 << 18) + 5, 3 * (1 << 18) + 1, (1 << 18) - 1, 2 << 18):
+        blob = rnd.randbytes(80 * n)
+        got = b"".join(miner.hash_headers([blob[80 * i:80 * i + 80] for i in range(n)]))
+        assert got == oracle.hash_headers(blob), n
+
+
 def test_hash_header_single(miner, oracle):
     h = miner.parse_header(bytes.fromhex(W.GENESIS_HEADER_HEX))
     assert miner.hash_header(h).hex() == W.GENESIS_HASH_HEX
