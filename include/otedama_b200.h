@@ -97,10 +97,10 @@ int otd_meets_target(const uint8_t hash[32], uint32_t nbits);
 
 /* GPU batch form of miner.HashHeader / miner.SHA256d on 80-byte inputs
  * (sha256d.go:107-117): hashes n serialised headers (host pointers) on
- * `device_index`, writes n*32 bytes.  Chunks of 2^18 headers are pipelined
- * through pinned staging and device buffers that are allocated on the first call
- * for a device and kept.  Throughput is bound by the host-side copies of the
- * caller's pageable buffers, not by the kernel; one call at a time per device. */
+ * `device_index`, writes n*32 bytes.  Chunks of 2^18 headers are pipelined over
+ * two streams through device buffers that are allocated on the first call for a
+ * device and kept.  Throughput is bound by the host-side copies of the caller's
+ * pageable buffers, not by the kernel; one call at a time per device. */
 int otd_hash_headers(int device_index, const uint8_t* headers80, size_t n, uint8_t* hashes32);
 
 /* ------------------------------------------------------------------- work --

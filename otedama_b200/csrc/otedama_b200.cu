@@ -1245,16 +1245,16 @@ extern "C" int otd_prepare_instances(int device_index, const otd_work_t* work, u
 }
 
 // ------------------------------------------------------------ hash_headers --
-// Batch HashHeader.  The caller's buffers are ordinary (pageable) host memory, so the call is a pipeline of
-// chunks through two pinned staging slots per device: host copy in -> cudaMemcpyAsync -> kernel ->
-// cudaMemcpyAsync -> host copy out, chunk i+1's copy-in overlapping chunk i on the device.  Device buffers and
-// staging are allocated once per device and kept (no cudaMalloc/cudaFree per call).  The kernel itself runs at
-// billions of headers per second; end to end the entry point is bound by the host-side copies.
+// Batch HashHeader.  The caller's buffers are ordinary (pageable) host memory.  The call walks them in chunks
+// over two streams with two device buffer pairs that are allocated once per device and kept (no
+// cudaMalloc/cudaFree per call): the driver's own staged copy of chunk i+1 overlaps chunk i's kernel and
+// copy-out.  The kernel itself runs at billions of headers per second; end to end the entry point is bound by
+// the host-side copies of pageable memory (an extra hop through library-owned pinned staging was
+// measured and is slower than letting the driver stage: 82 vs 98+ M headers/s).
 namespace {
 struct HashStage {
     static const size_t kChunk = 1u << 18;  // headers per chunk: 20 MiB in, 8 MiB out
     uint8_t *d_in[2] = {nullptr, nullptr}, *d_out[2] = {nullptr, nullptr};
-    uint8_t *h_in[2] = {nullptr, nullptr}, *h_out[2] = {nullptr, nullptr};
     cudaStream_t st[2] = {nullptr, nullptr};
     bool ready = false;
     std::mutex mu;
@@ -1264,8 +1264,6 @@ struct HashStage {
         for (int k = 0; k < 2; k++) {
             CU_TRY(cudaMalloc(&d_in[k], 80 * kChunk));
             CU_TRY(cudaMalloc(&d_out[k], 32 * kChunk));
-            CU_TRY(cudaMallocHost(&h_in[k], 80 * kChunk));
-            CU_TRY(cudaMallocHost(&h_out[k], 32 * kChunk));
             CU_TRY(cudaStreamCreateWithFlags(&st[k], cudaStreamNonBlocking));
         }
         ready = true;
@@ -1291,27 +1289,20 @@ extern "C" int otd_hash_headers(int device_index, const uint8_t* headers80, size
         if (!g_hash_stage[device_index]) g_hash_stage[device_index].reset(new HashStage());
         hs = g_hash_stage[device_index].get();
     }
-    std::lock_guard<std::mutex> g(hs->mu);  // one call at a time per device: the staging slots are shared
+    std::lock_guard<std::mutex> g(hs->mu);  // one call at a time per device: the device buffers are shared
     if ((rc = hs->init())) return rc;
     const size_t nchunks = (n + HashStage::kChunk - 1) / HashStage::kChunk;
-    size_t pending_off[2] = {0, 0}, pending_cnt[2] = {0, 0};
-    for (size_t c = 0; c < nchunks + 2; c++) {
+    for (size_t c = 0; c < nchunks; c++) {
         const int k = (int)(c & 1);
-        if (pending_cnt[k]) {  // the chunk that used this slot two steps ago: wait for it and hand its digests over
-            CU_TRY(cudaStreamSynchronize(hs->st[k]));
-            memcpy(hashes32 + 32 * pending_off[k], hs->h_out[k], 32 * pending_cnt[k]);
-            pending_cnt[k] = 0;
-        }
-        if (c >= nchunks) continue;
         const size_t off = c * HashStage::kChunk, cnt = std::min(HashStage::kChunk, n - off);
-        memcpy(hs->h_in[k], headers80 + 80 * off, 80 * cnt);
-        CU_TRY(cudaMemcpyAsync(hs->d_in[k], hs->h_in[k], 80 * cnt, cudaMemcpyHostToDevice, hs->st[k]));
+        // stream order protects the slot: this chunk's copy-in queues behind the copy-out of chunk c-2
+        CU_TRY(cudaMemcpyAsync(hs->d_in[k], headers80 + 80 * off, 80 * cnt, cudaMemcpyHostToDevice, hs->st[k]));
         hash_headers_kernel<<<(unsigned)((cnt + 127) / 128), 128, 0, hs->st[k]>>>(hs->d_in[k], cnt, hs->d_out[k]);
         CU_TRY(cudaGetLastError());
-        CU_TRY(cudaMemcpyAsync(hs->h_out[k], hs->d_out[k], 32 * cnt, cudaMemcpyDeviceToHost, hs->st[k]));
-        pending_off[k] = off;
-        pending_cnt[k] = cnt;
+        CU_TRY(cudaMemcpyAsync(hashes32 + 32 * off, hs->d_out[k], 32 * cnt, cudaMemcpyDeviceToHost, hs->st[k]));
     }
+    CU_TRY(cudaStreamSynchronize(hs->st[0]));
+    CU_TRY(cudaStreamSynchronize(hs->st[1]));
     return OTD_OK;
 }
 

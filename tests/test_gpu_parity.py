@@ -72,8 +72,8 @@ def test_hash_headers_matches_oracle(miner, oracle, n):
 
 
 def test_hash_headers_across_staging_chunks(miner, oracle):
-    """The entry point pipelines chunks of 2^18 headers through two pinned staging slots: ragged multi-chunk
-    batches (1, 2 and 3+ chunks, back to back so slots are reused dirty) against the oracle."""
+    """The entry point pipelines chunks of 2^18 headers over two streams and two kept device buffer pairs: ragged
+    multi-chunk batches (1, 2 and 3+ chunks, back to back so slots are reused dirty) against the oracle."""
     rnd = random.Random(77)
     for n in ((1 << 18) + 5, 3 * (1 << 18) + 1, (1 << 18) - 1, 2 << 18):
         blob = rnd.randbytes(80 * n)
