@@ -101,6 +101,7 @@ template <int V> OTD_HD vw<V> maj(const vw<V>& a, const vw<V>& b, const vw<V>& c
 // into a vector register).
 // ---------------------------------------------------------------------------
 #define OTD_KN_Z_EIGHTHS(n) ((unsigned)(n) << 16)
+#define OTD_KN_ZSEL(s) ((unsigned)(s) << 28)
 enum : unsigned {
     KN_E = 1u,       // e' = d + t1                 as IMAD
     KN_HKW = 2u,     // h + K + W                   as 2 IMAD instead of IADD3
@@ -260,7 +261,17 @@ struct Ops {
     {
         return ((KN >> KN_Z_SHIFT) & 15u) ? ((KN >> KN_Z_SHIFT) & 15u) : 8u;
     }
-    OTD_HD static constexpr bool z_round(uint32_t k) { return ((k >> 7) & 7u) < z_eighths(); }
+    // Which rounds: three bits of the round constant starting at bit 7 + 2 * KN_ZSEL (bits 28..31 of KN; 0 = the
+    // shipped subset).  The subsets are equivalent in opcode mix; they differ in the order ptxas ends up with.
+    OTD_HD static constexpr unsigned z_shift()
+    {
+        static_assert(((KN >> 28) & 15u) <= 12u, "KN_ZSEL: the 3-bit window must stay inside the 32-bit constant");
+        return 7u + 2u * ((KN >> 28) & 15u);
+    }
+    OTD_HD static constexpr bool z_round(uint32_t k)
+    {
+        return (((k >> z_shift()) | (k << (32u - z_shift()))) & 7u) < z_eighths();
+    }
     // same with K + W a job constant or an immediate
     OTD_HD uint32_t t1_k(uint32_t h, uint32_t e, uint32_t f, uint32_t g, uint32_t k) const
     {

@@ -38,7 +38,8 @@ struct VsParams;
     X(7, "h_add_sp", 1, 16, OTD_KN_SPX, true, 5, 256)                                               \
     X(8, "x_z6_kc_b4", 1, 16, OTD_KN_BEST | otd::KN_KCONST, false, 4, 256)                          \
     X(9, "x_z6_t7z_b4", 1, 16, OTD_KN_BEST | otd::KN_T7Z, false, 4, 256)                            \
-    X(10, "x_z6_kc_t7z_b4", 1, 16, OTD_KN_BEST | otd::KN_KCONST | otd::KN_T7Z, false, 4, 256)
+    X(10, "x_z6_kc_t7z_b4", 1, 16, OTD_KN_BEST | otd::KN_KCONST | otd::KN_T7Z, false, 4, 256)                      \
+    X(11, "x_z6_s3", 1, 16, OTD_KN_BEST | OTD_KN_ZSEL(3), false, 4, 256)
 
 #define OTD_NUM_PRODUCTION_VARIANTS 6
 #define OTD_DEFAULT_VARIANT 0
