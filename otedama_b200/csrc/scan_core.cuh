@@ -122,6 +122,8 @@ enum : unsigned {
                      // Applied to KN_Z_EIGHTHS(n)/8 of the rounds (the rest use the KN_T1X form): the best
                      // FMA:ALU balance is an interior point (measured: 5/8..6/8).
     KN_Z_SHIFT = 16u,  // bits 16..19: n of KN_Z_EIGHTHS(n), 1..8
+    KN_LATE = 1u << 14,    // kernel level: the early-reject test of candidate i runs inside candidate i+1 (after its rounds
+                           // 4..6) instead of at the end of candidate i's dependency chain; the last one is flushed after the loop
     KN_KCONST = 1u << 26,  // rounds 16/17 of hash 1 (K + W is a job constant in the constant bank): fixed one-IADD3 form.
                            // Without it the KN_T1Z placement of these two rounds is picked from the VALUE of the
                            // constant, i.e. by a run-time (uniform) branch over two copies of the round
@@ -485,8 +487,13 @@ OTD_HD vw<V> hash2_e60(const Ops<KN>& op, const vw<V>& x0, const vw<V>& x1, cons
 // HALF (performance experiments only, never shipped as a scan variant's result):
 // stop after hash 1 and return its digest word 7 minus IV7, so that instruction
 // placement can be studied on a body that fits the instruction cache.
-template <int V, unsigned KN, bool HALF = false>
-OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
+struct NoHook {
+    OTD_HD void operator()() const {}
+};
+// `hook` runs once, early in hash 1 (after rounds 4..6): the kernel's KN_LATE form parks the previous candidate's
+// early-reject test there, away from the end of the dependency chain.
+template <int V, unsigned KN, bool HALF = false, class Hook = NoHook>
+OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op, Hook&& hook = Hook())
 {
     vw<V> w[64];
     vw<V> a, b, c, d, e, f, g, h;
@@ -511,6 +518,7 @@ OTD_HD vw<V> scan_core(const JobConsts& jc, const vw<V>& w3, const Ops<KN>& op)
         vw<V> a4 = a, e4 = e;
         a = a7; b = a6; c = a5; d = a4; e = e7; f = e6; g = e5; h = e4;
     }
+    hook();
     // rounds 7..15: W5..W14 = 0, W15 = 0x280
     rnd(op, a, b, c, d, e, f, g, h, Kc(7));
     rnd(op, h, a, b, c, d, e, f, g, Kc(8));

@@ -83,15 +83,8 @@ scan_kernel(const __grid_constant__ JobConsts jc, const __grid_constant__ PipeMu
     constexpr unsigned long long kTile = (unsigned long long)BLOCK * V * ITER;
     const unsigned long long tile0 = (unsigned long long)blockIdx.x * kTile + threadIdx.x;
 
-#pragma unroll 1
-    for (int it = 0; it < ITER; it++) {
-        const unsigned long long idx0 = tile0 + (unsigned long long)it * (BLOCK * V);
-        vw<V> w3;
-#pragma unroll
-        for (int v = 0; v < V; v++)
-            w3.x[v] = __byte_perm(nonce_begin + (uint32_t)idx0 + (uint32_t)(v * BLOCK), 0, 0x0123);
-        const vw<V> e60 = (KN & KN_COMPACT) ? scan_core_compact<V, KN>(jc, w3, op) : scan_core<V, KN, HALF>(jc, w3, op);
-
+    // early-reject test + rare path for the V candidates whose e60 words are `e60`, first index `idx0`
+    auto test = [&](const vw<V>& e60, unsigned long long idx0) {
         unsigned cmask = 0;
 #pragma unroll
         for (int v = 0; v < V; v++) {
@@ -115,7 +108,27 @@ scan_kernel(const __grid_constant__ JobConsts jc, const __grid_constant__ PipeMu
                 ring_push_warp(hit, nonce, instance, dig, ring, entries, cap);
             }
         }
+    };
+
+    vw<V> pend = bc<V>(0u);  // KN_LATE: the previous iteration's result, tested inside the next one
+#pragma unroll 1
+    for (int it = 0; it < ITER; it++) {
+        const unsigned long long idx0 = tile0 + (unsigned long long)it * (BLOCK * V);
+        vw<V> w3;
+#pragma unroll
+        for (int v = 0; v < V; v++)
+            w3.x[v] = __byte_perm(nonce_begin + (uint32_t)idx0 + (uint32_t)(v * BLOCK), 0, 0x0123);
+        if (KN & KN_LATE) {
+            const vw<V> cur = scan_core<V, KN, HALF>(jc, w3, op, [&] {
+                if (it > 0) test(pend, idx0 - (unsigned long long)(BLOCK * V));
+            });
+            pend = cur;
+        } else {
+            const vw<V> e60 = (KN & KN_COMPACT) ? scan_core_compact<V, KN>(jc, w3, op) : scan_core<V, KN, HALF>(jc, w3, op);
+            test(e60, idx0);
+        }
     }
+    if (KN & KN_LATE) test(pend, tile0 + (unsigned long long)(ITER - 1) * (BLOCK * V));
     if (threadIdx.x == 0) atomicAdd(&ring->blocks_done, 1u);
 }
 

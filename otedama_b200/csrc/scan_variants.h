@@ -39,7 +39,10 @@ struct VsParams;
     X(8, "x_z6_kc_b4", 1, 16, OTD_KN_BEST | otd::KN_KCONST, false, 4, 256)                          \
     X(9, "x_z6_t7z_b4", 1, 16, OTD_KN_BEST | otd::KN_T7Z, false, 4, 256)                            \
     X(10, "x_z6_kc_t7z_b4", 1, 16, OTD_KN_BEST | otd::KN_KCONST | otd::KN_T7Z, false, 4, 256)                      \
-    X(11, "x_z6_s3", 1, 16, OTD_KN_BEST | OTD_KN_ZSEL(3), false, 4, 256)
+    X(11, "x_z6_s3", 1, 16, OTD_KN_BEST | OTD_KN_ZSEL(3), false, 4, 256)                            \
+    X(12, "x_z6_late_b4", 1, 16, OTD_KN_BEST | otd::KN_LATE, false, 4, 256)                          \
+    X(13, "x_z6_late_s3_b4", 1, 16, OTD_KN_BEST | otd::KN_LATE | OTD_KN_ZSEL(3), false, 4, 256)      \
+    X(14, "x_z6_late_t7z_b4", 1, 16, OTD_KN_BEST | otd::KN_LATE | otd::KN_T7Z, false, 4, 256)
 
 #define OTD_NUM_PRODUCTION_VARIANTS 6
 #define OTD_DEFAULT_VARIANT 0

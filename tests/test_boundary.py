@@ -212,6 +212,7 @@ def test_work_validation_errors(product):
         (dict(version_mask=0x6000, version_begin=4), "version_begin outside"),
         (dict(version_mask=0x6000, version_count=5), "version_count exceeds"),
         (dict(version_mask=0x6000, version_begin=1, version_stride=2, version_count=3), "version_count exceeds"),
+        (dict(version_mask=0xFFFFFFFF), "larger than 2^31 indices"),       # 2^32 indices would wrap the device's 32-bit index
         (dict(ok, extranonce2_size=17), "extranonce2_size > 16"),
         (dict(ok, extranonce2_count=0), "extranonce2_count must be >= 1"),
         (dict(ok, extranonce2_size=1, extranonce2_count=257), "does not fit extranonce2_size"),
@@ -226,6 +227,7 @@ def test_work_validation_errors(product):
             engine.partition_work(miner.Work(**fields), 0, 1)
     # and the same work with consistent fields passes
     for fields in (dict(nonce_begin=0xFFFFFFFF, nonce_count=1), dict(version_mask=0x6000, version_begin=3),
+                   dict(version_mask=0xFFFFFFFF, version_count=1 << 31), dict(version_mask=0x7FFFFFFF),
                    dict(version_mask=0x6000, version_begin=1, version_stride=2, version_count=2),
                    dict(ok, extranonce2_size=1, extranonce2_count=256), dict(ok, extranonce2_size=0, extranonce2_count=1)):
         engine.partition_work(miner.Work(**fields), 0, 1)
