@@ -19,7 +19,7 @@ ap.add_argument("--seconds", type=float, default=60)
 a = ap.parse_args()
 rnd = random.Random(7)
 t = (1 << 238).to_bytes(32, "little")
-jobs, shares, switches = {}, 0, 0
+jobs, shares, switches, rolled_shares = {}, 0, 0, 0
 bad = 0
 rss0 = None
 t0 = time.time()
@@ -30,19 +30,32 @@ with miner.Worker(miner.WorkerConfig(launch_log2=24)) as w:
         else:
             i = rnd.randrange(1, 257)
             f = W.config2_fields(i)
+            roll = {}
+            if rnd.random() < 0.4:   # BIP-320 rolled work: goes through the version-shared kernel (groups of <= 32)
+                roll = dict(version_mask=W.BIP320_MASK, version_begin=rnd.randrange(0, 60000),
+                            version_count=rnd.choice([1, 2, 5, 32, 33, 70]), version_stride=rnd.choice([1, 3]))
             seq = w.set_work(miner.Work(job_id=switches & 0xFFFFFFFF, header=miner.Header(**f), target=t,
                                         repeat=rnd.random() < 0.5, nonce_begin=rnd.randrange(0, 1 << 31),
-                                        nonce_count=1 << rnd.randrange(16, 30)))
-            jobs[seq] = (switches & 0xFFFFFFFF, i)
+                                        nonce_count=1 << rnd.randrange(16, 30), **roll))
+            jobs[seq] = (switches & 0xFFFFFFFF, i, roll)
         switches += 1
         time.sleep(rnd.choice([0, 0.0005, 0.002, 0.01]))
         for s in w.poll_shares(256, 0):
             shares += 1
             ok = s.work_seq in jobs and jobs[s.work_seq][0] == s.job_id
-            if ok and shares % 50 == 0:
+            if ok:
                 f = W.config2_fields(jobs[s.work_seq][1])
-                oh = o.Header(f["version"], f["prev_hash"], f["merkle_root"], f["time"], f["bits"], s.nonce)
-                ok = o.hash_header(oh) == s.hash and o.less_or_equal(s.hash, t)
+                roll = jobs[s.work_seq][2]
+                if roll:   # the version must be one of the slice's
+                    want = {o.bip320_version(f["version"], W.BIP320_MASK, roll["version_begin"] + k * roll["version_stride"])
+                            for k in range(roll["version_count"])}
+                    ok = s.version in want
+                    rolled_shares += 1
+                else:
+                    ok = s.version == f["version"]
+                if ok and shares % 50 == 0:
+                    oh = o.Header(s.version, f["prev_hash"], f["merkle_root"], f["time"], f["bits"], s.nonce)
+                    ok = o.hash_header(oh) == s.hash and o.less_or_equal(s.hash, t)
             bad += not ok
         if switches == 2000:
             rss0 = resource.getrusage(resource.RUSAGE_SELF).ru_maxrss
@@ -51,7 +64,7 @@ with miner.Worker(miner.WorkerConfig(launch_log2=24)) as w:
                 del jobs[k]
     st = w.stats()
 rss1 = resource.getrusage(resource.RUSAGE_SELF).ru_maxrss
-print(f"{switches} set_work calls in {time.time() - t0:.0f} s, {shares} shares, {bad} bad, "
+print(f"{switches} set_work calls in {time.time() - t0:.0f} s, {shares} shares ({rolled_shares} of rolled works), {bad} bad, "
       f"hashes {st.hashes_total:.3e}, dropped {st.shares_dropped}, maxrss {rss0} -> {rss1} KiB")
 assert bad == 0 and shares > 0
 assert rss0 is None or rss1 - rss0 < 50_000, "host memory grew"
