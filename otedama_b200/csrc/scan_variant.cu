@@ -1,5 +1,7 @@
 // scan_variant.cu — one scan-kernel variant per translation unit: compile with
 // -DOTD_VIDX=<index into OTD_SCAN_VARIANTS>.
+#include <cstdlib>
+
 #include "scan_kernel.cuh"
 #include "scan_variants.h"
 
@@ -16,7 +18,18 @@ cudaError_t launch(const otd::JobConsts& jc, uint32_t nonce_begin, unsigned long
     constexpr unsigned long long tile = (unsigned long long)BLOCK * V * ITER;
     const unsigned grid = (unsigned)((count + tile - 1) / tile);
     if (grid == 0) return cudaSuccess;
-    otd::scan_kernel<V, ITER, KN, HALF, MINB, BLOCK><<<grid, BLOCK, 0, st>>>(jc, otd::make_pipe_mults(), nonce_begin, count,
+    // Occupancy experiment (performance studies only): OTD_K1_DYNSMEM=<bytes> of unused dynamic shared memory per
+    // block lowers the number of resident blocks per SM without touching the code (DESIGN.md §3.2 point 4).
+    static const int dyn = [] {
+        const char* e = getenv("OTD_K1_DYNSMEM");
+        return e ? atoi(e) : 0;
+    }();
+    if (dyn > 0) {
+        cudaError_t e = cudaFuncSetAttribute(otd::scan_kernel<V, ITER, KN, HALF, MINB, BLOCK>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, dyn);
+        if (e != cudaSuccess) return e;
+    }
+    otd::scan_kernel<V, ITER, KN, HALF, MINB, BLOCK><<<grid, BLOCK, dyn, st>>>(jc, otd::make_pipe_mults(), nonce_begin, count,
                                                                       instance, hdr, ent, cap, stop, gen);
     return cudaGetLastError();
 }
