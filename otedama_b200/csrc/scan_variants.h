@@ -58,6 +58,8 @@ struct VsParams;
 //   2 blocks/SM (b2) 9.98 | 128-thread blocks x 6 10.88, x 5 9.71 | 192 x 6 10.55 | ITER 2 / 8 11.16 / 11.19.
 // Three 256-thread blocks per SM (24 warps, 56 registers) are enough and slightly better than four; more warps
 // buy nothing, fewer (16) lose 12 %.  16 instances per launch instead of 32: 11.10 (z7_r7_b4).
+// Per-instance constants added as IMADs (cf, 14 fewer ALU instructions per hash): 11.355 — no gain, like every other
+// IMAD that needs a vector-register 1 (profiles/r2_vs_cfma.log).
 // Hash-1 rounds 24..63 rolled into an 8-round loop body (l1, 39 KB of code instead of 47): 10.96-11.05 — the
 // instruction cache is not what holds the kernel back (ncu: hit rate 93 %, no_instruction 0.3 of 10.6 cycles per issue).
 #define OTD_VS_VARIANTS(Y)                                  \
@@ -65,7 +67,8 @@ struct VsParams;
     Y(1, "vs_z7_r7_b4", 4, OTD_KN_VS(7, 7), 4, 256)         \
     Y(2, "vs_z6_r8_b3", 4, OTD_KN_VS(6, 0), 3, 256)         \
     Y(3, "vs_z7_r7_f20_b5", 4, OTD_KN_VS(7, 7) | otd::KN_VS_F20, 5, 256) \
-    Y(4, "vs_z7_r8_l1_b4", 4, OTD_KN_VS(7, 0) | otd::KN_VS_LOOP1, 4, 256)
+    Y(4, "vs_z7_r8_l1_b4", 4, OTD_KN_VS(7, 0) | otd::KN_VS_LOOP1, 4, 256) \
+    Y(5, "vs_z7_r8_cf_b3", 4, OTD_KN_VS(7, 0) | otd::KN_VS_CFMA, 3, 256)
 #define OTD_DEFAULT_VS_VARIANT 0
 
 typedef cudaError_t (*otd_scan_launch_fn)(const otd::JobConsts&, uint32_t nonce_begin,

@@ -34,6 +34,8 @@ enum : unsigned {
                          // IADD3 (h + Sigma1 + kw) on the ALU pipe — the FMA:ALU balance knob of scan_core.cuh's
                          // KN_T1Z, for rounds that need no immediate
     KN_VS_F20 = 1u << 24,  // see vs_first_round()
+    KN_VS_CFMA = 1u << 15,  // per-instance job constants (midstate words, round 3..6 folding) added as IMADs on the FMA pipe
+                            // instead of IADD with a uniform-register operand on the ALU pipe
     KN_VS_LOOP1 = 1u << 25,  // hash 1 rounds 24..63 as five trips of one 8-round body instead of 40 unrolled rounds:
                              // these rounds carry no schedule window (K+W comes from shared memory), so rolling
                              // them costs no registers and takes ~10 KB off the instruction-cache footprint
@@ -61,6 +63,13 @@ struct VsOps : Ops<KN> {
         }
         const uint32_t hk = this->add_if(KN & KN_HKW, h, kw);
         return this->add3_if(KN & KN_T1, hk, this->S1(e), ch(e, f, g));
+    }
+    // x + c for a per-instance job constant c
+    OTD_HD vw<1> vadd(const vw<1>& x, uint32_t c) const
+    {
+        vw<1> r;
+        r.x[0] = (KN & KN_VS_CFMA) ? fma_add(x.x[0], c, this->one_v) : x.x[0] + c;  // one_v: the constant is the one non-vector operand
+        return r;
     }
     // a round whose K + W is a job constant (constant bank): the placement must not be picked from the value
     // (that would be a run-time branch), so the one-IADD3 form is used whenever t1 is split at all
@@ -131,17 +140,17 @@ OTD_HD uint32_t vs_hash(const JobConsts& jv, const JobConsts& js, uint32_t w3s, 
     const W w3 = bc<1>(w3s);
     W a, b, c, d, e, f, g, h;
     // state after round 3 (rounds 0..2 folded per instance by K2 / the host)
-    a = w3 + jv.ca3;      b = bc<1>(jv.a3); c = bc<1>(jv.b3); d = bc<1>(jv.c3);
-    e = w3 + jv.ce3;      f = bc<1>(jv.e3); g = bc<1>(jv.f3); h = bc<1>(jv.g3);
+    a = op.vadd(w3, jv.ca3); b = bc<1>(jv.a3); c = bc<1>(jv.b3); d = bc<1>(jv.c3);
+    e = op.vadd(w3, jv.ce3); f = bc<1>(jv.e3); g = bc<1>(jv.f3); h = bc<1>(jv.g3);
     {
-        W t1 = cadd(op, padd(op, vS1(op, e), ch(e, f, g)), jv.k4);                      // round 4
-        W e5 = cadd(op, t1, jv.c3);
+        W t1 = op.vadd(padd(op, vS1(op, e), ch(e, f, g)), jv.k4);                       // round 4
+        W e5 = op.vadd(t1, jv.c3);
         W a5 = padd(op, padd(op, t1, vS0(op, a)), maj(a, b, c));
-        t1 = cadd(op, padd(op, vS1(op, e5), ch(e5, e, f)), jv.k5);                      // round 5
-        W e6 = cadd(op, t1, jv.b3);
+        t1 = op.vadd(padd(op, vS1(op, e5), ch(e5, e, f)), jv.k5);                       // round 5
+        W e6 = op.vadd(t1, jv.b3);
         W a6 = padd(op, padd(op, t1, vS0(op, a5)), maj(a5, a, b));
-        t1 = cadd(op, padd(op, vS1(op, e6), ch(e6, e5, e)), jv.k6);                     // round 6
-        W e7 = cadd(op, t1, jv.a3);
+        t1 = op.vadd(padd(op, vS1(op, e6), ch(e6, e5, e)), jv.k6);                      // round 6
+        W e7 = op.vadd(t1, jv.a3);
         W a7 = padd(op, padd(op, t1, vS0(op, a6)), maj(a6, a5, a));
         W a4 = a, e4 = e;
         a = a7; b = a6; c = a5; d = a4; e = e7; f = e6; g = e5; h = e4;
@@ -199,9 +208,9 @@ OTD_HD uint32_t vs_hash(const JobConsts& jv, const JobConsts& js, uint32_t w3s, 
 #undef OTD_VS_R8
 #undef OTD_VS_R
     // the role order now is (h,a,b,c,d,e,f,g) = (A,B,C,D,E,F,G,H); hash 2 on the digest (state + midstate)
-    return hash2_e60<1, KN>(op, cadd(op, h, jv.mid[0]), cadd(op, a, jv.mid[1]), cadd(op, b, jv.mid[2]),
-                            cadd(op, c, jv.mid[3]), cadd(op, d, jv.mid[4]), cadd(op, e, jv.mid[5]),
-                            cadd(op, f, jv.mid[6]), cadd(op, g, jv.mid[7]))
+    return hash2_e60<1, KN>(op, op.vadd(h, jv.mid[0]), op.vadd(a, jv.mid[1]), op.vadd(b, jv.mid[2]),
+                            op.vadd(c, jv.mid[3]), op.vadd(d, jv.mid[4]), op.vadd(e, jv.mid[5]),
+                            op.vadd(f, jv.mid[6]), op.vadd(g, jv.mid[7]))
         .x[0];
 }
 
