@@ -17,6 +17,13 @@ resident before the timed region.  `e2e` = the same through the worker C ABI
 integer-issue roofline measured live on the same GPU; `cpu_baseline` is the CPU
 restatement of the reference's grind loop on this box's host cores.
 
+Without a torchrun environment `--gpus N` (N > 1) drives N devices from ONE process — one host thread,
+worker and stream per device, the way the Go engine would (north_star) — and prints the same line
+(`arm.launch_mode` says which mode ran).  After the timed spans the shares of every timed header that
+has a committed full CPU scan (tests/golden/) are compared bit-exactly (`parity_checked`, `parity_ok`;
+a mismatch fails the run), and `rolled` reports the BIP-320 version-rolled workload (configs[3]) through
+the version-shared kernel beside the configs[1] headline.
+
 --impl reference times the reference's CPU arithmetic (the oracle port: serialise
 + 3 compressions per nonce, all host threads); the Go reference itself cannot be
 built here (no Go toolchain), so there is no oracle/_ref.
@@ -244,11 +251,89 @@ def main():
         build.build()          # no-op when the in-tree .so matches the sources (content hash)
     if dist:
         dist.barrier()         # nobody loads the library while rank 0 might still be linking it
-    from otedama_b200 import capi, miner, workloads as W
+    from otedama_b200 import capi
     ndev = capi.check(capi.lib().otd_device_count())
     if ndev <= 0:
         raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
-    dev = local % ndev
+
+    if dist:
+        comm = _DistComm(dist)
+        code = run_rank(args, rank, world, local % ndev, comm, "one process per GPU (torchrun)")
+        dist.barrier()
+        dist.destroy_process_group()
+    elif args.gpus > 1:
+        # No torchrun environment: ONE process drives --gpus devices, one host thread + worker + stream per device
+        # (what the Go engine does with one goroutine per device).  The C calls release the GIL.
+        n = min(args.gpus, ndev)
+        comm = _ThreadComm(n)
+        codes = [0] * n
+
+        def body(g):
+            codes[g] = run_rank(args, g, n, g, comm, "one process, one host thread per GPU")
+
+        threads = [threading.Thread(target=body, args=(g,)) for g in range(n)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        code = max(codes)
+    else:
+        code = run_rank(args, 0, 1, local % ndev, _NullComm(), "single GPU")
+    if code:
+        raise SystemExit("bench.py: share sets differ from the committed full scans (see stderr)")
+
+
+class _NullComm:
+    def barrier(self):
+        pass
+
+    def reduce(self, x, op):
+        return x
+
+
+class _DistComm:
+    def __init__(self, dist):
+        self.dist = dist
+
+    def barrier(self):
+        self.dist.barrier()
+
+    def reduce(self, x, op):
+        import torch
+        t = torch.tensor([float(x)], dtype=torch.float64)
+        self.dist.all_reduce(t, op=getattr(self.dist.ReduceOp, op))
+        return float(t[0])
+
+
+class _ThreadComm:
+    """Barrier + max/sum across the device threads of one process."""
+
+    def __init__(self, n):
+        self.n = n
+        self.bar = threading.Barrier(n)
+        self.lock = threading.Lock()
+        self.vals = []
+
+    def barrier(self):
+        self.bar.wait()
+
+    def reduce(self, x, op):
+        with self.lock:
+            self.vals.append(float(x))
+        self.bar.wait()
+        out = max(self.vals) if op == "MAX" else sum(self.vals)
+        if self.bar.wait() == 0:
+            self.vals = []
+        self.bar.wait()
+        return out
+
+
+def run_rank(args, rank, world, dev, comm, launch_mode):
+    """One rank's share of the bench (a process under torchrun, a thread in the one-process mode); rank 0 prints.
+    Returns non-zero when a timed header's share set differs from its committed full scan."""
+    from otedama_b200 import capi, miner, workloads as W
+    dist = world > 1
+    barrier, reduce = comm.barrier, comm.reduce
     variant = args.variant if args.variant >= 0 else miner.default_variant()
     vname = miner.scan_variants()[variant]
     target = miner.target_from_difficulty(1.0)
@@ -261,18 +346,6 @@ def main():
     my_steps = [header(i) for i in walk]
     warm, timed = my_steps[:args.warmup], my_steps[args.warmup:]
     timed_idx = walk[args.warmup:]
-
-    def barrier():
-        if dist:
-            dist.barrier()
-
-    def reduce(x, op):
-        if not dist:
-            return x
-        import torch
-        t = torch.tensor([float(x)], dtype=torch.float64)
-        dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
-        return float(t[0])
 
     # ---- kernel leg: inputs resident, one CUDA-event pair around the K launches ----
     if warm:
@@ -400,7 +473,7 @@ def main():
                 "warmup": args.warmup, "ms_per_step": dev_ms / max(1, args.steps), "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
                 "config": config_dict(world),
-                "arm": {"kernel_variant": vname, "shares_found": shares_found,
+                "arm": {"kernel_variant": vname, "launch_mode": launch_mode, "shares_found": shares_found,
                         "timed_headers_rank0": [timed_idx[0], timed_idx[-1]]},
                 "parity_checked": n_checked, "parity_ok": n_bad == 0,
                 "parity_note": ("timed headers with a committed full-2^32 CPU scan (tests/golden/): share sets of the "
@@ -412,11 +485,7 @@ def main():
         if cpu:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
-    if dist:
-        dist.barrier()
-        dist.destroy_process_group()
-    if n_bad:
-        raise SystemExit("bench.py: share sets differ from the committed full scans (see stderr)")
+    return 1 if n_bad else 0
 
 
 if __name__ == "__main__":
