@@ -388,6 +388,29 @@ int otd_vs_variants(char (*names)[32], int max_names);
 int otd_vs_default_variant(void);
 int otd_vs_select(int variant);
 
+/* The launch plan of a work: how one pass over its search space is cut into kernel
+ * launches — (first instance, instances in the launch, nonce window) — exactly as
+ * otd_scan and the worker do it.  Pure host arithmetic, no device needed; exposed so
+ * that the partition of the space can be property-tested on a CPU box (every
+ * (instance, nonce) in exactly one launch; a version-shared launch holds at most
+ * OTD_VS_MAX_INSTANCES instances of ONE extranonce2 value).  No reference counterpart
+ * (one goroutine strides one header's nonces, internal/miner/worker.go:248-280).
+ * launch_log2 as in otd_worker_config_t (0 = 32).  Writes up to max_launches entries,
+ * returns how many; *n_launches (may be NULL) gets the total, which walks the whole
+ * plan — bound the work's space when asking for it. */
+#define OTD_VS_MAX_INSTANCES 32u
+typedef struct {
+    uint64_t first_instance;      /* instance = (extranonce2 index) * versions_per_extranonce2 + version slot */
+    uint32_t n_instances;         /* consecutive instances in this launch */
+    uint32_t version_shared;      /* 1 = version-shared kernel, 0 = plain kernel */
+    uint32_t nonce_begin;
+    uint32_t version_index_first; /* BIP-320 index of the first instance (0 without a mask) */
+    uint64_t nonce_count;
+    uint64_t extranonce2;         /* value of the launch's instances (0 without a coinbase) */
+} otd_launch_plan_t;
+int otd_plan_launches(const otd_work_t* work, uint32_t launch_log2, otd_launch_plan_t* out,
+                      uint32_t max_launches, uint64_t* n_launches);
+
 /* Job-preparation kernels exposed for parity tests (K3: extranonce2 roll +
  * coinbase hash + merkle fold; K2: rolled version). Fills n merkle roots
  * (32 bytes each) / n versions for the work's first n instances. */

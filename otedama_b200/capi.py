@@ -77,6 +77,12 @@ class CV1Submit(Structure):
                 ("version_bits_hex", c_char * 9), ("job_id", c_char * OTD_JOB_ID_MAX)]
 
 
+class CLaunchPlan(Structure):
+    _fields_ = [("first_instance", c_uint64), ("n_instances", c_uint32), ("version_shared", c_uint32),
+                ("nonce_begin", c_uint32), ("version_index_first", c_uint32), ("nonce_count", c_uint64),
+                ("extranonce2", c_uint64)]
+
+
 class CWorkerConfig(Structure):
     _fields_ = [("ring_capacity", c_uint32), ("queue_capacity", c_uint32), ("launch_log2", c_uint32),
                 ("kernel_variant", c_int32)]
@@ -131,6 +137,7 @@ _SIGS = {
                                  POINTER(c_uint64)]),
     "otd_scan_variants": (c_int, [c_void_p, c_int]),
     "otd_scan_default_variant": (c_int, []),
+    "otd_plan_launches": (c_int, [POINTER(CWork), c_uint32, POINTER(CLaunchPlan), c_uint32, POINTER(c_uint64)]),
     "otd_vs_variants": (c_int, [c_void_p, c_int]),
     "otd_vs_default_variant": (c_int, []),
     "otd_vs_select": (c_int, [c_int]),

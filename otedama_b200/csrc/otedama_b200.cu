@@ -690,6 +690,32 @@ static int copy_work(const otd_work_t* in, WorkCopy* wc)
     return OTD_OK;
 }
 
+// How one run cuts a work's (instance x nonce) space into kernel launches.  Pure host arithmetic, shared by
+// Engine::run and otd_plan_launches (which exposes it to CPU-side property tests).
+struct LaunchGroup {
+    uint32_t grp;     // version instances in the launch (1 = plain kernel)
+    bool shared;      // version-shared kernel
+    uint64_t step;    // nonces per launch
+};
+static const uint32_t kPrepBatch = 256;  // instances prepared (K3/K2) at a time
+// `inst`: absolute instance index; `left_in_batch`: instances from inst to the end of its preparation batch;
+// `vs_tile` / `plain_tile`: nonces per thread block of the two kernels (vs_tile 0 = sharing switched off).
+static LaunchGroup plan_group(const WorkCopy& wc, uint64_t inst, uint32_t left_in_batch, uint64_t chunk,
+                              uint64_t vs_tile, uint64_t plain_tile)
+{
+    LaunchGroup g{1, false, chunk};
+    (void)plain_tile;
+    // Version instances of one extranonce2 value share block 2 of hash 1: up to kVsMaxVersions of them go into
+    // ONE version-shared launch (scan_vs_kernel.cuh) — never across extranonce2 values (different merkle roots)
+    // nor across a preparation batch; a lone instance takes the plain kernel.
+    if (vs_tile && wc.w.version_mask)
+        g.grp = (uint32_t)std::min<uint64_t>({(uint64_t)kVsMaxVersions, wc.n_ver - inst % wc.n_ver, (uint64_t)left_in_batch});
+    g.shared = g.grp >= 2;
+    // nonces per launch: the configured candidate count split over the group, in whole blocks
+    if (g.shared) g.step = std::max(vs_tile, chunk / g.grp / vs_tile * vs_tile);
+    return g;
+}
+
 extern "C" int otd_work_partition(const otd_work_t* in, uint32_t g, uint32_t G, otd_work_t* out)
 {
     if (!in || !out || G == 0 || g >= G) return fail(OTD_EINVAL, "otd_work_partition: bad argument");
@@ -715,6 +741,47 @@ extern "C" int otd_work_partition(const otd_work_t* in, uint32_t g, uint32_t G, 
     }
     *out = w;
     return OTD_OK;
+}
+
+extern "C" int otd_plan_launches(const otd_work_t* work, uint32_t launch_log2, otd_launch_plan_t* out,
+                                 uint32_t max_launches, uint64_t* n_launches)
+{
+    WorkCopy wc;
+    int rc = copy_work(work, &wc);
+    if (rc) return rc;
+    if (max_launches && !out) return fail(OTD_EINVAL, "otd_plan_launches: out is NULL");
+    if (launch_log2 == 0) launch_log2 = 32;
+    launch_log2 = std::min(32u, std::max(16u, launch_log2));
+    const uint64_t chunk = 1ull << launch_log2;
+    const VsVariant* const vs = (wc.w.flags & OTD_WORK_PER_VERSION_LAUNCH) ? nullptr : vs_variant_in_use();
+    const ScanVariant& kv = kVariants[kDefaultVariant];
+    uint64_t n = 0;
+    uint32_t written = 0;
+    for (uint64_t bf = 0; bf < wc.n_inst; bf += kPrepBatch) {
+        const uint32_t nb = (uint32_t)std::min<uint64_t>(kPrepBatch, wc.n_inst - bf);
+        for (uint32_t i = 0; i < nb;) {
+            const LaunchGroup lg = plan_group(wc, bf + i, nb - i, chunk, vs ? (uint64_t)vs->block * vs->iter : 0,
+                                              (uint64_t)kv.block * kv.v * kv.iter);
+            for (uint64_t off = 0; off < wc.nonce_count; off += lg.step) {
+                if (written < max_launches) {
+                    otd_launch_plan_t& p = out[written++];
+                    p.first_instance = bf + i;
+                    p.n_instances = lg.grp;
+                    p.version_shared = lg.shared ? 1 : 0;
+                    p.nonce_begin = wc.w.nonce_begin + (uint32_t)off;
+                    p.nonce_count = std::min(lg.step, wc.nonce_count - off);
+                    p.extranonce2 = wc.has_coinbase ? wc.w.extranonce2_begin + ((bf + i) / wc.n_ver) * wc.en2_stride : 0;
+                    p.version_index_first = wc.w.version_begin + (uint32_t)((bf + i) % wc.n_ver) * wc.ver_stride;
+                }
+                n++;
+                if (n > (1ull << 40)) return fail(OTD_ERANGE, "otd_plan_launches: more than 2^40 launches");
+            }
+            i += lg.grp;
+        }
+        if (written >= max_launches && !n_launches) break;  // nothing more to report
+    }
+    if (n_launches) *n_launches = n;
+    return (int)written;
 }
 
 extern "C" int otd_share_to_v1_submit(const otd_share_t* share, uint32_t extranonce2_size, uint32_t version_mask,
@@ -764,7 +831,7 @@ struct Slot {
 
 class Engine {
    public:
-    static const uint32_t kBatch = 256;
+    static const uint32_t kBatch = kPrepBatch;
     int dev = -1;
     uint32_t cap = 0;
     cudaStream_t stream = nullptr, aux = nullptr;
@@ -1007,15 +1074,12 @@ class Engine {
             for (uint32_t i = 0; i < nb && !abort_sent && !halted;) {
                 const uint64_t inst = bf + i;
                 const uint64_t en2 = wc.w.extranonce2_begin + (inst / wc.n_ver) * wc.en2_stride;
-                // Version instances of one extranonce2 value share block 2 of hash 1: up to kVsMaxVersions of
-                // them go into ONE version-shared launch (scan_vs_kernel.cuh); a lone instance takes the plain kernel.
-                uint32_t grp = 1;
-                if (vs && wc.w.version_mask)
-                    grp = (uint32_t)std::min<uint64_t>({(uint64_t)kVsMaxVersions, wc.n_ver - inst % wc.n_ver, (uint64_t)(nb - i)});
-                const bool shared = grp >= 2;
+                const LaunchGroup lg = plan_group(wc, inst, nb - i, chunk, vs ? (uint64_t)vs->block * vs->iter : 0,
+                                                  (uint64_t)kv.block * kv.v * kv.iter);
+                const uint32_t grp = lg.grp;
+                const bool shared = lg.shared;
+                const uint64_t step = lg.step;
                 const uint64_t blk_nonces = shared ? (uint64_t)vs->block * vs->iter : (uint64_t)kv.block * kv.v * kv.iter;
-                // nonces per launch: the configured candidate count split over the group, in whole blocks
-                const uint64_t step = shared ? std::max(blk_nonces, chunk / grp / blk_nonces * blk_nonces) : chunk;
                 VsParams vp;
                 if (shared) memcpy(vp.jc, &h_consts[i], sizeof(JobConsts) * grp);
                 for (uint64_t off = 0; off < wc.nonce_count; off += step) {

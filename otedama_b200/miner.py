@@ -268,6 +268,19 @@ def default_variant() -> int:
     return int(lib().otd_scan_default_variant())
 
 
+def plan_launches(work: Work, launch_log2: int = 0, max_launches: int = 1 << 16):
+    """The kernel launches one pass over `work` is cut into (otd_plan_launches): a list of
+    (first_instance, n_instances, version_shared, nonce_begin, nonce_count, extranonce2, version_index_first)
+    and the total number of launches.  Host arithmetic only — works without a device."""
+    cw, keep = work._c()
+    out = (capi.CLaunchPlan * max(1, max_launches))()
+    total = ctypes.c_uint64()
+    n = check(lib().otd_plan_launches(ctypes.byref(cw), launch_log2, out, max_launches, ctypes.byref(total)))
+    del keep
+    return [(p.first_instance, p.n_instances, bool(p.version_shared), p.nonce_begin, p.nonce_count, p.extranonce2,
+             p.version_index_first) for p in out[:n]], total.value
+
+
 def vs_variants() -> List[str]:
     """Version-shared scan variants (used for work that rolls BIP-320 version bits)."""
     return capi.names_list(lib().otd_vs_variants)

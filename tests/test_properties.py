@@ -112,3 +112,45 @@ def test_partition_is_a_partition(product, G, begin, stride, count, axis):
     assert sorted(seen) == whole
     with pytest.raises(engine.EngineError):
         engine.partition_work(w, G, G)
+
+
+# -- the launch plan: one pass over a work = kernel launches that tile its (instance x nonce) space exactly once ------
+@settings(max_examples=250, deadline=None)
+@given(st.integers(0, 90), st.integers(0, 12), st.integers(1, 5), st.integers(0, 5000), st.integers(1, 1 << 22),
+       st.sampled_from([16, 18, 20, 32]), st.booleans(), st.integers(0, 9), st.integers(1, 3))
+def test_launch_plan_tiles_the_search_space(product, n_ver, n_en2, ver_stride, nonce_begin, nonce_count, launch_log2,
+                                            per_version, en2_begin, en2_stride):
+    """otd_plan_launches (the arithmetic Engine::run launches by): every (instance, nonce) of the work in exactly one
+    launch; a version-shared launch holds 2..OTD_VS_MAX_INSTANCES version instances of ONE extranonce2 value and of
+    one 256-instance preparation batch, with consecutive version indices; lone instances take the plain kernel;
+    OTD_WORK_PER_VERSION_LAUNCH switches sharing off."""
+    from otedama_b200 import miner
+    kw = dict(target=b"\xff" * 32, nonce_begin=nonce_begin, nonce_count=nonce_count, per_version_launch=per_version)
+    if n_ver:
+        kw.update(version_mask=0x1FFFE000, version_begin=3, version_stride=ver_stride, version_count=n_ver)
+    if n_en2:
+        kw.update(coinb1=b"\x01\x02", extranonce2_size=4, extranonce2_begin=en2_begin, extranonce2_stride=en2_stride,
+                  extranonce2_count=n_en2)
+    vers, en2s = max(1, n_ver), max(1, n_en2)
+    plan, total = miner.plan_launches(miner.Work(**kw), launch_log2)
+    assert total == len(plan)
+    covered = {}
+    for first, n, shared, nb, nc, en2, vidx in plan:
+        assert 1 <= n <= 32 and shared == (n >= 2) and nc >= 1
+        if per_version or not n_ver:
+            assert n == 1
+        e_idx, slot = divmod(first, vers)
+        assert slot + n <= vers                                   # one extranonce2 value per launch
+        assert first // 256 == (first + n - 1) // 256             # one preparation batch per launch
+        assert en2 == (en2_begin + e_idx * en2_stride if n_en2 else 0)
+        assert vidx == (3 + slot * ver_stride if n_ver else 0)
+        assert nonce_begin <= nb and nb + nc <= nonce_begin + nonce_count
+        for inst in range(first, first + n):
+            covered.setdefault(inst, []).append((nb, nb + nc))
+    assert sorted(covered) == list(range(vers * en2s))
+    for inst, spans in covered.items():                           # the nonce windows of an instance tile its range
+        spans.sort()
+        assert spans[0][0] == nonce_begin and spans[-1][1] == nonce_begin + nonce_count
+        assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+    # a launch never exceeds the configured candidate count by more than one block of the version-shared kernel
+    assert all(n * nc <= max(1 << launch_log2, n * 1024) for _, n, _, _, nc, _, _ in plan)
