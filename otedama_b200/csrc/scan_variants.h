@@ -53,7 +53,9 @@ struct VsParams;
 #define OTD_KN_VS(n, m) (OTD_KN_ADDS | otd::KN_SP | otd::KN_T1Z | OTD_KN_Z_EIGHTHS(n) | OTD_KN_VSZ_EIGHTHS(m))
 // Measured on B200 (profiles/r2_vs_sweep_*.log), GH/s per GPU, 32 version instances x 2^27 nonces per launch
 // (the plain kernel launched once per version: 9.52):
-//   vs_z7_r8_b3 11.365 (shipped) | z6_r8_b3 11.364 | z7_r7_b3 11.35 | z8_r8_b3 11.33 | z7_r8_b4 11.33 | z7_r7_b4 11.21 |
+//   vs_z7_r8_s5_b3 11.455 (shipped: z7_r8_b3 with another choice of WHICH eighth of the immediate-constant rounds keeps
+//   its IADD3 — KN_ZSEL 5; the other eleven choices 11.27-11.37, profiles/r2_vs_zsel*.log: an order lottery, see
+//   DESIGN.md §3.2 point 5) | vs_z7_r8_b3 11.365 | z6_r8_b3 11.364 | z7_r7_b3 11.35 | z8_r8_b3 11.33 | z7_r8_b4 11.33 | z7_r7_b4 11.21 |
 //   z6_r8_b4 11.19 | f20_b5 (5 blocks/SM) 11.19 | z6_r6_b4 11.11 | z7_r5_b4 11.07 | z8_r7_b4 11.02 |
 //   2 blocks/SM (b2) 9.98 | 128-thread blocks x 6 10.88, x 5 9.71 | 192 x 6 10.55 | ITER 2 / 8 11.16 / 11.19.
 // Three 256-thread blocks per SM (24 warps, 56 registers) are enough and slightly better than four; more warps
@@ -63,12 +65,13 @@ struct VsParams;
 // Hash-1 rounds 24..63 rolled into an 8-round loop body (l1, 39 KB of code instead of 47): 10.96-11.05 — the
 // instruction cache is not what holds the kernel back (ncu: hit rate 93 %, no_instruction 0.3 of 10.6 cycles per issue).
 #define OTD_VS_VARIANTS(Y)                                  \
-    Y(0, "vs_z7_r8_b3", 4, OTD_KN_VS(7, 0), 3, 256)         \
-    Y(1, "vs_z7_r7_b4", 4, OTD_KN_VS(7, 7), 4, 256)         \
+    Y(0, "vs_z7_r8_s5_b3", 4, OTD_KN_VS(7, 0) | OTD_KN_ZSEL(5), 3, 256) \
+    Y(1, "vs_z7_r8_b3", 4, OTD_KN_VS(7, 0), 3, 256)         \
     Y(2, "vs_z6_r8_b3", 4, OTD_KN_VS(6, 0), 3, 256)         \
     Y(3, "vs_z7_r7_f20_b5", 4, OTD_KN_VS(7, 7) | otd::KN_VS_F20, 5, 256) \
     Y(4, "vs_z7_r8_l1_b4", 4, OTD_KN_VS(7, 0) | otd::KN_VS_LOOP1, 4, 256) \
-    Y(5, "vs_z7_r8_cf_b3", 4, OTD_KN_VS(7, 0) | otd::KN_VS_CFMA, 3, 256)
+    Y(5, "vs_z7_r8_cf_b3", 4, OTD_KN_VS(7, 0) | otd::KN_VS_CFMA, 3, 256) \
+    Y(6, "vs_z7_r7_b4", 4, OTD_KN_VS(7, 7), 4, 256)
 #define OTD_DEFAULT_VS_VARIANT 0
 
 typedef cudaError_t (*otd_scan_launch_fn)(const otd::JobConsts&, uint32_t nonce_begin,

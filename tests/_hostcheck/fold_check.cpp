@@ -78,6 +78,7 @@ int fc_vs_e60_kn(const uint8_t hdr76[76], const uint32_t* versions, int n_ver, u
         case VSSET(7, 7): run_vs<VSSET(7, 7)>(jcs, n_ver, nonce, e60_out); return 0;
         case VSSET(8, 0): run_vs<VSSET(8, 0)>(jcs, n_ver, nonce, e60_out); return 0;
         case VSSET(7, 0): run_vs<VSSET(7, 0)>(jcs, n_ver, nonce, e60_out); return 0;
+        case VSSET(7, 0) | OTD_KN_ZSEL(5): run_vs<VSSET(7, 0) | OTD_KN_ZSEL(5)>(jcs, n_ver, nonce, e60_out); return 0;
         case VSSET(7, 0) | KN_VS_CFMA: run_vs<VSSET(7, 0) | KN_VS_CFMA>(jcs, n_ver, nonce, e60_out); return 0;
         case VSSET(8, 7): run_vs<VSSET(8, 7)>(jcs, n_ver, nonce, e60_out); return 0;
         case VSSET(7, 6): run_vs<VSSET(7, 6)>(jcs, n_ver, nonce, e60_out); return 0;

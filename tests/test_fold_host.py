@@ -119,18 +119,20 @@ VS_KNOB_SETS = [0, 1023, ADDS | KN["T1X"] | KN["SP"], VSSET(6, 0), VSSET(6, 6), 
                 VSSET(7, 7), VSSET(8, 0), VSSET(7, 7) | (1 << 24), VSSET(6, 6) | (1 << 24),
                 VSSET(7, 7) | (1 << 25), VSSET(7, 0) | (1 << 25), VSSET(7, 7) | (3 << 24),
                 VSSET(7, 0), VSSET(6, 7), VSSET(7, 6), VSSET(5, 7), VSSET(7, 5), VSSET(8, 7), VSSET(6, 0),
-                VSSET(7, 0) | (1 << 15)]
+                VSSET(7, 0) | (1 << 15), VSSET(7, 0) | (5 << 28)]
 
 
 def test_every_version_shared_variant_policy_is_host_checked():
     """Each version-shared scan variant's knob set (csrc/scan_variants.h, OTD_VS_VARIANTS) is exercised below."""
     import re
     txt = open(os.path.join(HERE, "..", "otedama_b200", "csrc", "scan_variants.h")).read()
-    rows = re.findall(r"Y\((\d+), \"(\w+)\", (\d+), OTD_KN_VS\((\d+), (\d+)\)((?: \| otd::KN_VS_\w+)*), \d+, \d+\)", txt)
+    rows = re.findall(r"Y\((\d+), \"(\w+)\", (\d+), OTD_KN_VS\((\d+), (\d+)\)((?: \| (?:otd::KN_VS_\w+|OTD_KN_ZSEL\(\d+\)))*), \d+, \d+\)", txt)
     assert len(rows) == len(re.findall(r"^\s*Y\(\d+,", txt, flags=re.M)) > 0, "unparsed version-shared variant rows"
     for idx, name, it, n, m, extra in rows:
         bits = ((1 << 24) if "KN_VS_F20" in extra else 0) | ((1 << 25) if "KN_VS_LOOP1" in extra else 0) | \
                ((1 << 15) if "KN_VS_CFMA" in extra else 0)
+        zsel = re.search(r"OTD_KN_ZSEL\((\d+)\)", extra)
+        bits |= (int(zsel.group(1)) << 28) if zsel else 0
         assert VSSET(int(n), int(m)) | bits in VS_KNOB_SETS, name
 
 
