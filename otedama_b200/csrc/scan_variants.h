@@ -58,8 +58,9 @@ struct VsParams;
 //   DESIGN.md §3.2 point 5) | vs_z7_r8_b3 11.365 | z6_r8_b3 11.364 | z7_r7_b3 11.35 | z8_r8_b3 11.33 | z7_r8_b4 11.33 | z7_r7_b4 11.21 |
 //   z6_r8_b4 11.19 | f20_b5 (5 blocks/SM) 11.19 | z6_r6_b4 11.11 | z7_r5_b4 11.07 | z8_r7_b4 11.02 |
 //   2 blocks/SM (b2) 9.98 | 128-thread blocks x 6 10.88, x 5 9.71 | 192 x 6 10.55 | ITER 2 / 8 11.16 / 11.19.
-// Three 256-thread blocks per SM (24 warps, 56 registers) are enough and slightly better than four; more warps
-// buy nothing, fewer (16) lose 12 %.  16 instances per launch instead of 32: 11.10 (z7_r7_b4).
+// b3 = __launch_bounds__(256, 3): a register cap of 85, of which ptxas uses 56 — four blocks per SM stay resident
+// (ncu: 49.5 % of the warp slots), the looser cap only buys a better schedule than b4's 64 (48 used); b5 buys
+// nothing, b2 (more registers, fewer resident blocks) loses 12 %.  16 instances per launch instead of 32: 11.10 (z7_r7_b4).
 // Per-instance constants added as IMADs (cf, 14 fewer ALU instructions per hash): 11.355 — no gain, like every other
 // IMAD that needs a vector-register 1 (profiles/r2_vs_cfma.log).
 // Hash-1 rounds 24..63 rolled into an 8-round loop body (l1, 39 KB of code instead of 47): 10.96-11.05 — the

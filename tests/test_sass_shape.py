@@ -70,13 +70,14 @@ def vs_sass(product):
 
 
 def test_version_shared_kernel_resources(vs_sass):
-    """No spills; registers within the budget of three 256-thread blocks per SM (the shipped launch bounds); the
-    46-word schedule column per thread is the only shared memory (3 x 47,104 B fit the SM's 228 KB)."""
+    """No spills; registers at most 64, so that four 256-thread blocks stay resident per SM although the shipped
+    launch bounds (256, 3) would allow 85; the 46-word schedule column per thread is the only shared memory
+    (4 x 47,104 B fit the SM's 228 KB)."""
     txt, _ = vs_sass
     m = re.search(r"Function _ZN3otd14scan_vs_kernel\S*:\s*\n\s*REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", txt)
     assert m, txt[:400]
     reg, stack, shared, local = map(int, m.groups())
-    assert reg <= 85 and local == 0 and stack <= 128
+    assert reg <= 64 and local == 0 and stack <= 128
     assert shared - 46 * 256 * 4 in (0, 1024)             # cuobjdump adds the 1 KB the driver reserves per block
 
 
