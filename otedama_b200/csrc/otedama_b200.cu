@@ -690,6 +690,7 @@ static int copy_work(const otd_work_t* in, WorkCopy* wc)
     return OTD_OK;
 }
 
+static_assert(OTD_VS_MAX_INSTANCES == (unsigned)kVsMaxVersions, "public constant out of step with the kernel's limit");
 // How one run cuts a work's (instance x nonce) space into kernel launches.  Pure host arithmetic, shared by
 // Engine::run and otd_plan_launches (which exposes it to CPU-side property tests).
 struct LaunchGroup {
