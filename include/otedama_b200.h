@@ -266,7 +266,8 @@ typedef struct {
     uint32_t ring_capacity;   /* device share ring entries per launch; 0 = 4096 */
     uint32_t queue_capacity;  /* host share queue (reference: chan cap Threads*4); 0 = 65536.
                                  Shares arriving at a full queue are dropped and counted. */
-    uint32_t launch_log2;     /* nonces per kernel launch = 2^launch_log2 (16..32); 0 = 32 */
+    uint32_t launch_log2;     /* candidates per kernel launch = 2^launch_log2 (16..32); 0 = 32.  A version-shared
+                                 launch of g instances covers 2^launch_log2 / g nonces (otd_plan_launches) */
     int32_t kernel_variant;   /* scan kernel variant, -1 = library default (see otd_scan_variants) */
 } otd_worker_config_t;
 
