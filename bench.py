@@ -418,6 +418,24 @@ def run_rank(args, rank, world, dev, comm, launch_mode):
     rolled_hashes = reduce(rr.hashes, "SUM")
     rolled_value = rolled_hashes / (rolled_ms * 1e-3) / 1e9
     rolled_launches = int(reduce(rr.launches, "SUM"))
+    # ... and end to end through the worker C ABI (host work struct in, shares out, wall clock)
+    w = miner.Worker(miner.WorkerConfig(device=dev)).start()
+    barrier()
+    r0 = time.time()
+    w.set_work(rolled_work)
+    w.wait_exhausted(-1)
+    rolled_e2e_shares = []
+    while True:
+        part = w.poll_shares(4096, 0)
+        if not part:
+            break
+        rolled_e2e_shares += part
+    barrier()
+    r1 = time.time()
+    w.stop()
+    rolled_e2e_s = reduce(r1 - r0, "MAX")
+    same = sorted((x.version, x.nonce, x.hash) for x in rolled_e2e_shares) == sorted((x.version, x.nonce, x.hash) for x in rr.shares)
+    rolled_same = int(reduce(0 if same else 1, "SUM")) == 0
 
     if rank == 0:
         # ---- roofline: measured integer-issue peaks on this GPU, same process ----
@@ -455,7 +473,9 @@ def run_rank(args, rank, world, dev, comm, launch_mode):
                                f"version instances per GPU x 2^{ROLLED_LOG2} nonces, difficulty 1, version index k -> rank "
                                f"k mod {world}"),
                   "value": rolled_value, "unit": UNIT, "kernel_variant": miner.vs_variants()[miner.default_vs_variant()],
-                  "ms": rolled_ms, "launches": rolled_launches, "shares_found": int(reduce(rr.found, "SUM")) if not dist else None,
+                  "ms": rolled_ms, "launches": rolled_launches,
+                  "e2e": {"value": rolled_hashes / rolled_e2e_s / 1e9, "unit": UNIT, "seconds": rolled_e2e_s,
+                          "same_shares_as_the_synchronous_scan": rolled_same}, "shares_found": int(reduce(rr.found, "SUM")) if not dist else None,
                   "alu_only_ops_per_hash": vs_ops,
                   "frac": rolled_value * 1e9 / world * vs_ops / peak_alu,
                   "note": ("version instances of one job share block 2 of hash 1, so its message schedule is expanded "
