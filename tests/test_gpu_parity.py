@@ -179,6 +179,21 @@ def test_all_ff_target_overflows_the_ring_without_hanging(miner):
     assert len({s.nonce for s in r.shares}) == len(r.shares)
 
 
+def test_all_ff_target_overflows_the_ring_in_a_version_shared_launch(miner, oracle):
+    """The same through K1v: every (version, nonce) of a 4-version launch is a share; the bounded ring keeps
+    65536 of them (distinct, correctly attributed to their version and re-hashing right), counts the rest."""
+    c4 = W.config4_v2()
+    r = miner.scan(miner.Work(header=mheader(miner, c4), target=b"\xff" * 32, version_mask=c4["mask"], version_count=4,
+                              nonce_count=1 << 16), max_shares=1 << 17)
+    assert r.launches == 1 and r.found == 4 << 16 and r.hashes == 4 << 16
+    assert len(r.shares) == 1 << 16 and len({(s.version, s.nonce) for s in r.shares}) == len(r.shares)
+    versions = {oracle.bip320_version(c4["version"], c4["mask"], k) for k in range(4)}
+    assert {s.version for s in r.shares} <= versions
+    for s in r.shares[::997]:
+        h = oracle.Header(s.version, c4["prev_hash"], c4["merkle_root"], s.ntime, c4["bits"], s.nonce)
+        assert oracle.hash_header(h) == s.hash
+
+
 def test_full_nonce_range_genesis(miner, golden):
     """configs[0]: full 2^32 scan must find exactly nonce 2083236893 — the same
     set the CPU oracle's full scan produced (tests/golden/genesis_full_scan.json)."""
