@@ -26,6 +26,11 @@ MAIN_SRC = os.path.join(CSRC, "otedama_b200.cu")
 VARIANT_SRC = os.path.join(CSRC, "scan_variant.cu")
 VS_VARIANT_SRC = os.path.join(CSRC, "scan_vs_variant.cu")
 
+# Performance studies only: extra nvcc flags for the version-shared variant objects (e.g. "-Xptxas -regUsageLevel=4")
+# and an alternative output path, so that differently compiled libraries can sit side by side (OTD_LIB selects one).
+VS_EXTRA_FLAGS = os.environ.get("OTD_VS_EXTRA_FLAGS", "").split()
+LIB_OUT = os.environ.get("OTD_LIB_OUT", "")
+
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",
@@ -54,6 +59,8 @@ def _digest(paths, extra="") -> str:
 def _compile(src, out, defines, log):
     nvcc = os.environ.get("NVCC", "nvcc")
     cmd = [nvcc] + NVCC_FLAGS + defines + ["-c", "-o", out, src]
+    if src == VS_VARIANT_SRC:
+        cmd[1:1] = VS_EXTRA_FLAGS
     proc = subprocess.run(cmd, capture_output=True, text=True)
     log.append(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
     if proc.returncode != 0:
@@ -76,6 +83,8 @@ def needs_build() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False, jobs: int = 0) -> str:
+    if LIB_OUT:
+        force = True      # a side-by-side experimental library: always (re)link, never touch the stamp
     if not force and not needs_build():
         return LIB_PATH
     os.makedirs(OBJ, exist_ok=True)
@@ -86,10 +95,10 @@ def build(force: bool = False, verbose: bool = False, jobs: int = 0) -> str:
     key_var = _digest(HEADERS[:3] + [HEADERS[5], VARIANT_SRC], " ".join(NVCC_FLAGS))
     for i in variant_indices():
         tasks.append((VARIANT_SRC, os.path.join(OBJ, f"variant{i}_{key_var}.o"), [f"-DOTD_VIDX={i}"]))
-    key_vs = _digest(HEADERS[:3] + HEADERS[5:8] + [VS_VARIANT_SRC], " ".join(NVCC_FLAGS))
+    key_vs = _digest(HEADERS[:3] + HEADERS[5:8] + [VS_VARIANT_SRC], " ".join(NVCC_FLAGS + VS_EXTRA_FLAGS))
     for i in vs_variant_indices():
         tasks.append((VS_VARIANT_SRC, os.path.join(OBJ, f"vsvariant{i}_{key_vs}.o"), [f"-DOTD_VSIDX={i}"]))
-    todo = [t for t in tasks if force or not os.path.exists(t[1])]
+    todo = [t for t in tasks if (force and not LIB_OUT) or not os.path.exists(t[1])]
     jobs = jobs or min(len(todo) or 1, os.cpu_count() or 1)
     with cf.ThreadPoolExecutor(max_workers=jobs) as ex:
         futs = [ex.submit(_compile, src, out, defs, log) for src, out, defs in todo]
@@ -98,21 +107,23 @@ def build(force: bool = False, verbose: bool = False, jobs: int = 0) -> str:
     keep = {t[1] for t in tasks}
     for f in os.listdir(OBJ):  # drop stale objects
         p = os.path.join(OBJ, f)
-        if p not in keep:
+        if p not in keep and not LIB_OUT and not VS_EXTRA_FLAGS:
             os.remove(p)
     nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH] + [t[1] for t in tasks] + ["-ldl"]
+    out_path = LIB_OUT or LIB_PATH
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", out_path] + [t[1] for t in tasks] + ["-ldl"]
     proc = subprocess.run(cmd, capture_output=True, text=True)
     log.append(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
     with open(os.path.join(_PKG, "build.log"), "w") as fh:
         fh.write("\n".join(log))
     if proc.returncode != 0:
         raise RuntimeError("link failed:\n" + proc.stdout + proc.stderr)
-    with open(STAMP_PATH, "w") as fh:
-        fh.write(source_hash() + "\n")
+    if not LIB_OUT:
+        with open(STAMP_PATH, "w") as fh:
+            fh.write(source_hash() + "\n")
     if verbose:
         print("\n".join(log))
-    return LIB_PATH
+    return out_path
 
 
 if __name__ == "__main__":

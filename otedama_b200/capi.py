@@ -13,7 +13,7 @@ from ctypes import (POINTER, Structure, c_char, c_char_p, c_double, c_int, c_int
                     c_size_t, c_uint8, c_uint32, c_uint64, c_void_p)
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libotedama_b200.so")
+LIB_PATH = os.environ.get("OTD_LIB") or os.path.join(_PKG, "libotedama_b200.so")   # OTD_LIB: performance studies
 HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "otedama_b200.h")
 
 OTD_OK, OTD_EINVAL, OTD_ENODEV, OTD_ENOMEM, OTD_EBUSY, OTD_ECUDA, OTD_ERANGE = 0, -22, -19, -12, -16, -5, -34
