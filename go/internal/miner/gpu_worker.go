@@ -16,6 +16,7 @@ import (
 	"errors"
 	"fmt"
 	"runtime"
+	"sync"
 	"sync/atomic"
 	"time"
 	"unsafe"
@@ -73,7 +74,7 @@ type GPUWorker struct {
 	done     chan struct{}
 	dropped  atomic.Uint64 // shares lost because the Go channel was full (worker.go:271-275 counts the same)
 	lastErr  atomic.Pointer[string]
-	en2Size  atomic.Uint32
+	en2Sizes sync.Map // work_seq (uint64) -> extranonce2_size (uint32) of that work; a share names its work_seq
 }
 
 // lastError runs a failing C call and reads otd_last_error() on the SAME OS thread: the message is
@@ -156,9 +157,12 @@ func (w *GPUWorker) StartGPU(ctx context.Context) <-chan GPUShare {
 					Nonce: uint32(buf[i].nonce), NTime: uint32(buf[i].ntime), Version: uint32(buf[i].version),
 					DeviceID: w.deviceID}
 				copy(s.Hash[:], C.GoBytes(unsafe.Pointer(&buf[i].hash[0]), 32))
-				g := GPUShare{Share: s, ExtraNonce2: uint64(buf[i].extranonce2),
-					ExtraNonce2Size: int(w.en2Size.Load()), JobIDStr: C.GoString(&buf[i].job_id_str[0]),
-					WorkSeq: uint64(buf[i].work_seq)}
+				size := 0 // of the work the share belongs to, not of whatever work is current by now
+				if v, ok := w.en2Sizes.Load(uint64(buf[i].work_seq)); ok {
+					size = int(v.(uint32))
+				}
+				g := GPUShare{Share: s, ExtraNonce2: uint64(buf[i].extranonce2), ExtraNonce2Size: size,
+					JobIDStr: C.GoString(&buf[i].job_id_str[0]), WorkSeq: uint64(buf[i].work_seq)}
 				select { // non-blocking send, like worker.go:271-275; a full channel is a counted drop
 				case shares <- g:
 				default:
@@ -211,9 +215,9 @@ func (w *GPUWorker) SetWorkExt(work *Work, ext *GPUWorkExt) error {
 	C.memcpy(unsafe.Pointer(&cw.target[0]), unsafe.Pointer(&work.Target[0]), 32)
 	var pin runtime.Pinner // the library copies every buffer before set_work returns
 	defer pin.Unpin()
+	en2Size := uint32(0)
 	if ext == nil {
 		cw.flags = C.OTD_WORK_REPEAT // the reference's endless rescan (worker.go:279)
-		w.en2Size.Store(0)
 	} else {
 		if ext.Repeat {
 			cw.flags = C.OTD_WORK_REPEAT
@@ -254,12 +258,20 @@ func (w *GPUWorker) SetWorkExt(work *Work, ext *GPUWorkExt) error {
 			cw.extranonce2_begin, cw.extranonce2_count = C.uint64_t(ext.ExtraNonce2Begin), C.uint64_t(ext.ExtraNonce2Count)
 			cw.extranonce2_stride = C.uint64_t(ext.ExtraNonce2Stride)
 		}
-		w.en2Size.Store(ext.ExtraNonce2Size)
+		if ext.Coinb1 != nil {
+			en2Size = ext.ExtraNonce2Size
+		}
 	}
 	runtime.LockOSThread()
 	defer runtime.UnlockOSThread()
-	if seq := C.otd_worker_set_work(w.h, &cw); seq < 0 {
+	seq := C.otd_worker_set_work(w.h, &cw)
+	if seq < 0 {
 		return fmt.Errorf("miner: gpu worker %s: %s", w.deviceID, C.GoString(C.otd_last_error()))
+	}
+	// shares of this work may still arrive after later SetWork calls; keep a short history
+	w.en2Sizes.Store(uint64(seq), en2Size)
+	if seq > 64 {
+		w.en2Sizes.Delete(uint64(seq) - 64)
 	}
 	return nil
 }
