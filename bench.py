@@ -45,7 +45,7 @@ sys.path.insert(0, ROOT)
 ALG_OPS_PER_HASH = 2450          # SHF 1176 + LOP3 628 + IADD3 646
 # Version-shared scan (BIP-320 rolled work, scripts/count_ops.py): shift/logic ops per (nonce, version) + per nonce / V
 VS_ALU_ONLY_PER_VERSION, VS_ALU_ONLY_PER_NONCE = 1500, 304
-ROLLED_VERSIONS, ROLLED_LOG2 = 32, 30     # the rolled leg: 32 versions x 2^30 nonces per rank
+ROLLED_VERSIONS, ROLLED_LOG2 = 64, 29     # the rolled leg: 64 versions x 2^29 nonces per rank
 GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
 METRIC = "sha256d_hashrate"
 UNIT = "GH/s"

@@ -379,7 +379,7 @@ int otd_scan_default_variant(void);
  * (version_mask != 0, at least two version instances in the slice) is searched by
  * a second kernel family: the versions of a job differ only in block 1 of the
  * header, so block 2's message schedule is expanded once per nonce and reused by
- * up to 16 version instances per launch (csrc/scan_vs_kernel.cuh).  No reference
+ * up to 64 version instances per launch (csrc/scan_vs_kernel.cuh).  No reference
  * counterpart: the reference ignores version rolling
  * (internal/poolproto/stratumv1/stratumv1.go:280-281).  The share set is the same
  * as with one plain launch per version (OTD_WORK_PER_VERSION_LAUNCH).
@@ -399,7 +399,7 @@ int otd_vs_select(int variant);
  * launch_log2 as in otd_worker_config_t (0 = 32).  Writes up to max_launches entries,
  * returns how many; *n_launches (may be NULL) gets the total, which walks the whole
  * plan — bound the work's space when asking for it. */
-#define OTD_VS_MAX_INSTANCES 32u
+#define OTD_VS_MAX_INSTANCES 64u
 typedef struct {
     uint64_t first_instance;      /* instance = (extranonce2 index) * versions_per_extranonce2 + version slot */
     uint32_t n_instances;         /* consecutive instances in this launch */

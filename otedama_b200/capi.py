@@ -21,6 +21,7 @@ OTD_WORK_REPEAT = 1
 OTD_WORK_PER_VERSION_LAUNCH = 2
 OTD_NOALLOC_MAX_SHARES = 4096
 OTD_JOB_ID_MAX = 64
+OTD_VS_MAX_INSTANCES = 64      # version instances per version-shared launch (include/otedama_b200.h)
 
 
 class OtdError(RuntimeError):

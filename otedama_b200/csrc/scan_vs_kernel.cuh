@@ -19,7 +19,7 @@
 
 namespace otd {
 
-constexpr int kVsMaxVersions = 32;  // instances per launch: 32 x 172 B of kernel parameters
+constexpr int kVsMaxVersions = 64;  // instances per launch: 64 x 172 B of kernel parameters
 
 struct VsParams {
     JobConsts jc[kVsMaxVersions];

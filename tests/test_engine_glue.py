@@ -443,7 +443,7 @@ def test_notify_to_submit_round_trip_with_rolled_versions(eng, oracle):
               "%08x" % c3["version"], "%08x" % c3["bits"], "%08x" % c3["time"], True]
     en1 = c3["extranonce1"].hex()
     w = engine.work_from_v1_notify(notify, en1, 4, 2.0 ** -16, chan_id=5, extranonce2_begin=0xFFFE, extranonce2_count=3)
-    w.version_mask, w.version_begin, w.version_count = mask, 40, 33           # 32 + a lone instance per extranonce2
+    w.version_mask, w.version_begin, w.version_count = mask, 40, 65           # 64 + a lone instance per extranonce2
     w.nonce_begin, w.nonce_count = 0xFFFF0000, 1 << 16
     assert (w.job_id, w.job_id_str) == (0, "1f9a")
     with miner.Worker() as wk:
@@ -470,7 +470,7 @@ def test_notify_to_submit_round_trip_with_rolled_versions(eng, oracle):
         h = oracle.Header(version, prev, coinbase_root, int(ntime_hex, 16), int(notify[6], 16), int(nonce_hex, 16))
         assert oracle.hash_header(h) == s.hash and oracle.less_or_equal(s.hash, target)
         seen_versions.add(version)
-    assert len(seen_versions) > 20
+    assert len(seen_versions) > 30
 
 
 # -- device allow-list, per-device configuration, pause by device id ---------------------------------

@@ -295,7 +295,7 @@ def test_version_rolling_matches_oracle(miner, oracle):
         sh, _, _ = oracle.grind(oh, t, 0x10000000, 1 << 16, threads=NCPU)
         want += okey(sh)
     r = miner.scan(work)
-    assert r.hashes == 40 << 16 and r.launches == 2       # version-shared launches of 32 + 8 instances
+    assert r.hashes == 40 << 16 and r.launches == 1       # one version-shared launch of the 40 instances
     assert key(r.shares) == sorted(want) and len(want) > 100
     assert all(s.job_id == 9 for s in r.shares)
     work.per_version_launch = True                        # the plain kernel, one launch per version instance
@@ -320,8 +320,10 @@ def test_version_rolling_default_count_covers_the_mask(miner, oracle):
 
 
 def test_version_shared_variants_match_oracle(miner, oracle):
-    """K1v (csrc/scan_vs_kernel.cuh): every version-shared variant, group sizes 2..32 incl. ragged tails
-    (33 = 32 + a lone instance on the plain kernel), ragged nonce windows, against the CPU oracle."""
+    """K1v (csrc/scan_vs_kernel.cuh): every version-shared variant, group sizes 2..64 incl. ragged tails
+    (65 = 64 + a lone instance on the plain kernel), ragged nonce windows, against the CPU oracle."""
+    from otedama_b200 import capi
+    VMAX = capi.OTD_VS_MAX_INSTANCES
     c4 = W.config4_v2()
     t = oracle.target_from_difficulty(2.0 ** -20)
     names = miner.vs_variants()
@@ -330,8 +332,8 @@ def test_version_shared_variants_match_oracle(miner, oracle):
         for vi, name in enumerate(names):
             miner.vs_select(vi)
             for n_ver, begin, stride, nb, nc in ((2, 0, 1, 0, 5000), (16, 7, 3, 0xFFFF0000, 1 << 16),
-                                                 (17, 100, 1, 123, 3 * 1024 + 1), (33, 65000, 16, 1 << 31, 4096)):
-                if vi and n_ver not in (17, 33):
+                                                 (33, 100, 1, 123, 3 * 1024 + 1), (VMAX + 1, 64000, 16, 1 << 31, 4096)):
+                if vi and n_ver not in (33, VMAX + 1):
                     continue
                 work = miner.Work(job_id=5, header=mheader(miner, c4), target=t, version_mask=c4["mask"],
                                   version_begin=begin, version_count=n_ver, version_stride=stride, nonce_begin=nb,
@@ -343,7 +345,7 @@ def test_version_shared_variants_match_oracle(miner, oracle):
                     want += okey(sh)
                 r = miner.scan(work)
                 assert r.hashes == n_ver * nc, (name, n_ver)
-                assert r.launches == (n_ver + 31) // 32
+                assert r.launches == (n_ver + VMAX - 1) // VMAX
                 assert key(r.shares) == sorted(want), (name, n_ver)
     finally:
         miner.vs_select(-1)

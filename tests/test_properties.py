@@ -116,7 +116,7 @@ def test_partition_is_a_partition(product, G, begin, stride, count, axis):
 
 # -- the launch plan: one pass over a work = kernel launches that tile its (instance x nonce) space exactly once ------
 @settings(max_examples=250, deadline=None)
-@given(st.integers(0, 90), st.integers(0, 12), st.integers(1, 5), st.integers(0, 5000), st.integers(1, 1 << 22),
+@given(st.integers(0, 150), st.integers(0, 12), st.integers(1, 5), st.integers(0, 5000), st.integers(1, 1 << 22),
        st.sampled_from([16, 18, 20, 32]), st.booleans(), st.integers(0, 9), st.integers(1, 3))
 def test_launch_plan_tiles_the_search_space(product, n_ver, n_en2, ver_stride, nonce_begin, nonce_count, launch_log2,
                                             per_version, en2_begin, en2_stride):
@@ -124,7 +124,7 @@ def test_launch_plan_tiles_the_search_space(product, n_ver, n_en2, ver_stride, n
     launch; a version-shared launch holds 2..OTD_VS_MAX_INSTANCES version instances of ONE extranonce2 value and of
     one 256-instance preparation batch, with consecutive version indices; lone instances take the plain kernel;
     OTD_WORK_PER_VERSION_LAUNCH switches sharing off."""
-    from otedama_b200 import miner
+    from otedama_b200 import capi, miner
     kw = dict(target=b"\xff" * 32, nonce_begin=nonce_begin, nonce_count=nonce_count, per_version_launch=per_version)
     if n_ver:
         kw.update(version_mask=0x1FFFE000, version_begin=3, version_stride=ver_stride, version_count=n_ver)
@@ -136,7 +136,7 @@ def test_launch_plan_tiles_the_search_space(product, n_ver, n_en2, ver_stride, n
     assert total == len(plan)
     covered = {}
     for first, n, shared, nb, nc, en2, vidx in plan:
-        assert 1 <= n <= 32 and shared == (n >= 2) and nc >= 1
+        assert 1 <= n <= capi.OTD_VS_MAX_INSTANCES and shared == (n >= 2) and nc >= 1
         if per_version or not n_ver:
             assert n == 1
         e_idx, slot = divmod(first, vers)
