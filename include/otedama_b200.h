@@ -398,7 +398,7 @@ int otd_vs_select(int variant);
  * (one goroutine strides one header's nonces, internal/miner/worker.go:248-280).
  * launch_log2 as in otd_worker_config_t (0 = 32).  Writes up to max_launches entries,
  * returns how many; *n_launches (may be NULL) gets the total, which walks the whole
- * plan — bound the work's space when asking for it. */
+ * plan: refused with OTD_ERANGE for a work of more than 2^22 instances. */
 #define OTD_VS_MAX_INSTANCES 64u
 typedef struct {
     uint64_t first_instance;      /* instance = (extranonce2 index) * versions_per_extranonce2 + version slot */

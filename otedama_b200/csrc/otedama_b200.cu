@@ -751,6 +751,9 @@ extern "C" int otd_plan_launches(const otd_work_t* work, uint32_t launch_log2, o
     int rc = copy_work(work, &wc);
     if (rc) return rc;
     if (max_launches && !out) return fail(OTD_EINVAL, "otd_plan_launches: out is NULL");
+    if (n_launches && wc.n_inst > (1ull << 22))
+        return fail(OTD_ERANGE, "otd_plan_launches: counting every launch of more than 2^22 instances is refused "
+                                "(pass n_launches = NULL for the first max_launches entries, or bound the work)");
     if (launch_log2 == 0) launch_log2 = 32;
     launch_log2 = std::min(32u, std::max(16u, launch_log2));
     const uint64_t chunk = 1ull << launch_log2;
@@ -775,7 +778,6 @@ extern "C" int otd_plan_launches(const otd_work_t* work, uint32_t launch_log2, o
                     p.version_index_first = wc.w.version_begin + (uint32_t)((bf + i) % wc.n_ver) * wc.ver_stride;
                 }
                 n++;
-                if (n > (1ull << 40)) return fail(OTD_ERANGE, "otd_plan_launches: more than 2^40 launches");
             }
             i += lg.grp;
         }

@@ -154,3 +154,17 @@ def test_launch_plan_tiles_the_search_space(product, n_ver, n_en2, ver_stride, n
         assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
     # a launch never exceeds the configured candidate count by more than one block of the version-shared kernel
     assert all(n * nc <= max(1 << launch_log2, n * 1024) for _, n, _, _, nc, _, _ in plan)
+
+
+def test_launch_plan_of_an_unbounded_work_is_cut_short_not_walked(product):
+    """A V1 work with every extranonce2 value (2^40 instances) would take forever to count: the total is refused,
+    the first entries are still available."""
+    import ctypes
+    from otedama_b200 import capi, miner
+    w = miner.Work(target=b"\xff" * 32, coinb1=b"\x01", extranonce2_size=8, extranonce2_count=1 << 40)
+    with pytest.raises(capi.OtdError, match="refused"):
+        miner.plan_launches(w)
+    cw, keep = w._c()
+    out = (capi.CLaunchPlan * 4)()
+    assert capi.lib().otd_plan_launches(ctypes.byref(cw), 0, out, 4, None) == 4
+    assert [out[i].extranonce2 for i in range(4)] == [0, 1, 2, 3] and out[0].nonce_count == 1 << 32
