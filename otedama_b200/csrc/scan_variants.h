@@ -64,6 +64,7 @@ struct VsParams;
 // Around the shipped variant (profiles/r2_vs_lottery3.log): ITER 1 / 2 / 8 10.15 / 11.18 / 11.44, 44 words (f20) under
 // b3 / b5 11.00 / 11.22, constant adds as IMADs 11.44 — nothing better.
 // 64 instances per launch instead of 32 (shipped since; profiles/r2_vs_v64.log): 11.490 (s5), 11.434 (z7_r8_b3).
+// -maxrregcount 50..64 changes nothing (launch bounds decide; profiles/r2_vs_maxrreg.log).
 // ptxas -regUsageLevel 0..4 = the default build (11.455), 6..10 11.24 (profiles/r2_vs_ptxas_ru.log).
 // Per-instance constants added as IMADs (cf, 14 fewer ALU instructions per hash): 11.355 — no gain, like every other
 // IMAD that needs a vector-register 1 (profiles/r2_vs_cfma.log).
