@@ -33,7 +33,8 @@ extern "C" {
 #define OTD_ECUDA (-5)
 #define OTD_ERANGE (-34)
 
-#define OTD_ABI_VERSION 2 /* 2: job_id_str in otd_work_t / otd_share_t, job_id in otd_v1_submit_t */
+#define OTD_ABI_VERSION 2 /* 2: job_id_str in otd_work_t / otd_share_t, job_id in otd_v1_submit_t,
+                             shared_launches in otd_stats_t */
 
 /* Last error message of the calling thread ("" if none). Never NULL. */
 const char* otd_last_error(void);
@@ -283,6 +284,7 @@ typedef struct {            /* miner.Stats, worker.go:79-86, plus device extras 
     uint64_t work_seq;        /* current set_work generation */
     int32_t has_work;         /* Worker.HasWork() */
     int32_t exhausted;        /* 1 when the current work's search space is finished */
+    uint64_t shared_launches; /* of `launches`: version-shared ones (BIP-320 rolled work, >= 2 instances each) */
 } otd_stats_t;
 
 /* NewWorker + Start (worker.go:111-151).  cfg may be NULL. Returns NULL on error. */

@@ -93,7 +93,7 @@ class CStats(Structure):
     _fields_ = [("hashes_total", c_uint64), ("shares_found", c_uint64), ("shares_dropped", c_uint64),
                 ("uptime_ns", c_uint64), ("hash_rate", c_double), ("launches", c_uint64),
                 ("candidates", c_uint64), ("device_ms", c_double), ("work_seq", c_uint64),
-                ("has_work", c_int32), ("exhausted", c_int32)]
+                ("has_work", c_int32), ("exhausted", c_int32), ("shared_launches", c_uint64)]
 
 
 _NAMES32 = (c_char * 32)

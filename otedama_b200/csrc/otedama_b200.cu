@@ -815,7 +815,7 @@ struct RunStats {
 
 struct ShareSink {
     virtual void on_share(const otd_share_t& s) = 0;
-    virtual void on_launch_done(uint64_t hashes, uint64_t candidates, double ms) = 0;
+    virtual void on_launch_done(uint64_t hashes, uint64_t candidates, double ms, bool version_shared) = 0;
     virtual ~ShareSink() {}
 };
 
@@ -1020,7 +1020,7 @@ class Engine {
         rs.kernel_ms += ms;
         rs.found += pushed;
         rs.ring_dropped += pushed - n;
-        sink.on_launch_done(hashed, s.h_hdr->candidates, ms);
+        sink.on_launch_done(hashed, s.h_hdr->candidates, ms, s.n_ver >= 2);
         for (uint32_t i = 0; i < n; i++) {
             otd_share_t sh;
             memset(&sh, 0, sizeof sh);
@@ -1136,7 +1136,7 @@ class Engine {
 struct CollectSink : ShareSink {
     std::vector<otd_share_t> shares;
     void on_share(const otd_share_t& s) override { shares.push_back(s); }
-    void on_launch_done(uint64_t, uint64_t, double) override {}
+    void on_launch_done(uint64_t, uint64_t, double, bool) override {}
 };
 
 static std::mutex g_pool_mu;
@@ -1387,7 +1387,7 @@ struct otd_worker : ShareSink {
     bool exhausted = false;
     uint64_t exhausted_reported = 0;  // work_seq whose end (exhausted or failed) a poll has already returned for
     std::deque<otd_share_t> queue;
-    std::atomic<uint64_t> hashes{0}, shares{0}, dropped{0}, launches{0}, candidates{0};
+    std::atomic<uint64_t> hashes{0}, shares{0}, dropped{0}, launches{0}, candidates{0}, shared_launches{0};
     double device_ms = 0;
     std::chrono::steady_clock::time_point t_start;
     std::string thread_error;
@@ -1403,10 +1403,11 @@ struct otd_worker : ShareSink {
         queue.push_back(s);
         cv_share.notify_all();
     }
-    void on_launch_done(uint64_t h, uint64_t c, double ms) override
+    void on_launch_done(uint64_t h, uint64_t c, double ms, bool version_shared) override
     {
         hashes.fetch_add(h);
         launches.fetch_add(1);
+        if (version_shared) shared_launches.fetch_add(1);
         candidates.fetch_add(c);
         std::lock_guard<std::mutex> g(mu);
         device_ms += ms;
@@ -1535,6 +1536,7 @@ extern "C" int otd_worker_stats(otd_worker_t* w, otd_stats_t* out)
     out->shares_found = w->shares.load();
     out->shares_dropped = w->dropped.load();
     out->launches = w->launches.load();
+    out->shared_launches = w->shared_launches.load();
     out->candidates = w->candidates.load();
     out->hash_rate = out->uptime_ns ? (double)out->hashes_total / ((double)out->uptime_ns * 1e-9) : 0.0;
     out->work_seq = w->seq.load();

@@ -206,6 +206,7 @@ class Stats:
     device_ms: float = 0.0
     work_seq: int = 0
     exhausted: bool = False
+    shared_launches: int = 0   # of `launches`: version-shared ones (rolled work)
 
 
 def _device_id(index: int) -> str:
@@ -384,7 +385,7 @@ class Worker:
         s = CStats()
         check(lib().otd_worker_stats(self._h, ctypes.byref(s)))
         return Stats(s.hashes_total, s.shares_found, s.shares_dropped, s.uptime_ns * 1e-9, s.hash_rate,
-                     s.launches, s.candidates, s.device_ms, s.work_seq, bool(s.exhausted))
+                     s.launches, s.candidates, s.device_ms, s.work_seq, bool(s.exhausted), s.shared_launches)
 
     def _need(self):
         if self._h is None:

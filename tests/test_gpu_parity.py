@@ -647,7 +647,7 @@ def test_worker_runs_rolled_work_like_the_synchronous_scan(miner, oracle):
         st = w.stats()
     assert key(got) == key(want.shares) and len(got) > 30
     # 9 groups of 5 version instances; 2^16 candidates per launch -> 12 blocks of 1024 nonces x 5, then the rest
-    assert st.hashes_total == want.hashes == 45 << 14 and st.launches == 18
+    assert st.hashes_total == want.hashes == 45 << 14 and st.launches == 18 and st.shared_launches == 18
     assert all(s.job_id == 77 for s in got)
     # and a few of them against the oracle, end to end
     for s in got[:5]:
